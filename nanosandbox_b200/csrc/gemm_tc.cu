@@ -1,0 +1,479 @@
+// bf16 GEMM on the 5th-gen tensor cores: C[M,N] = alpha * A[M,K] . B[N,K]^T, fp32 accumulate.
+//
+//   * operands staged by TMA (128-byte swizzle) into a STAGES-deep shared-memory ring,
+//   * tcgen05.mma (cta_group::1, UMMA 128 x BN x 16) issued by one thread, accumulators in TMEM,
+//     double-buffered (2 x BN columns) so the epilogue of tile i overlaps the mainloop of i+1,
+//   * persistent: one CTA per SM walks the tile list (m fastest: the A panel stays in L2),
+//   * K-major or MN-major operands (weight-gradient GEMMs read dY and X "transposed" in place
+//     through MN-major descriptors, no transpose pass),
+//   * split-K for the short-and-wide weight-gradient shapes (fp32 red.global.add epilogue),
+//   * fused epilogues (bias, exact GELU forward/backward, residual add, fp32 accumulate).
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..5 = epilogue (TMEM -> registers -> global), one TMEM lane quarter each.
+#include <mutex>
+#include <unordered_map>
+
+#include "gemm_common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace nsb {
+
+namespace {
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kThreads = 192;
+__host__ __device__ constexpr int stages_for(int bn) { return bn == 256 ? 4 : 6; }
+constexpr size_t smem_bytes_for(int bn) {
+  return static_cast<size_t>(stages_for(bn)) * (BM * BK * 2 + bn * BK * 2) + 1024 /*align*/ + 256 /*barriers*/;
+}
+}  // namespace
+
+// ---- epilogue: 32 consecutive columns of one output row held by one thread ---------------------
+__device__ __forceinline__ void epilogue_row32(const EpiParams& p, int m, int n, float* v, float alpha,
+                                               bool use_atomics) {
+  if (m >= p.M || n >= p.N) return;
+  const bool full = (n + 32 <= p.N);
+  const size_t o = static_cast<size_t>(m) * p.ldc + n;
+  const bool lowp_ok = full && ((p.ldc & 7) == 0);   // 16-byte aligned bf16 rows (n % 32 == 0)
+  const bool f32_ok = full && ((p.ldc & 3) == 0);
+  const bool has_bias = p.bias != nullptr && p.kind != NSB_EPI_ACCUM && p.kind != NSB_EPI_DGELU;
+
+  if (p.kind == NSB_EPI_ACCUM) {
+    if (!f32_ok) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        if (n + j >= p.N) continue;
+        float* c = static_cast<float*>(p.C) + o + j;
+        if (use_atomics) atomicAdd(c, v[j] * alpha);
+        else *c = p.accumulate ? *c + v[j] * alpha : v[j] * alpha;
+      }
+      return;
+    }
+    float4* c = reinterpret_cast<float4*>(static_cast<float*>(p.C) + o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float4 a = make_float4(v[4 * j] * alpha, v[4 * j + 1] * alpha, v[4 * j + 2] * alpha, v[4 * j + 3] * alpha);
+      if (use_atomics) {
+        atomicAdd(c + j, a);
+      } else {
+        if (p.accumulate) {
+          const float4 old = c[j];
+          a.x += old.x; a.y += old.y; a.z += old.z; a.w += old.w;
+        }
+        c[j] = a;
+      }
+    }
+    return;
+  }
+
+  const bool vec_ok = (p.kind == NSB_EPI_RESIDUAL) ? f32_ok : (p.c_bf16 ? lowp_ok : f32_ok);
+  if (!vec_ok) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) epilogue_scalar(p, m, n + j, v[j], alpha);
+    return;
+  }
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] *= alpha;
+  if (has_bias) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n) + j);
+      v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+    }
+  }
+  switch (p.kind) {
+    case NSB_EPI_STORE:
+    case NSB_EPI_GELU: {
+      if (p.c_bf16) {
+        uint4* c = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.C) + o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          c[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                            pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        if (p.kind == NSB_EPI_GELU) {
+          uint4* c2 = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.C2) + o);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_exact(round_bf16(v[j]));
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            c2[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                               pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        }
+      } else {
+        float4* c = reinterpret_cast<float4*>(static_cast<float*>(p.C) + o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        if (p.kind == NSB_EPI_GELU) {
+          float4* c2 = reinterpret_cast<float4*>(static_cast<float*>(p.C2) + o);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            c2[j] = make_float4(gelu_exact(v[4 * j]), gelu_exact(v[4 * j + 1]), gelu_exact(v[4 * j + 2]),
+                                gelu_exact(v[4 * j + 3]));
+        }
+      }
+      break;
+    }
+    case NSB_EPI_RESIDUAL: {
+      const float4* r = reinterpret_cast<const float4*>(static_cast<const float*>(p.aux) + o);
+      float4* c = reinterpret_cast<float4*>(static_cast<float*>(p.C) + o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 a = r[j];
+        if (p.c_bf16)
+          c[j] = make_float4(a.x + round_bf16(v[4 * j]), a.y + round_bf16(v[4 * j + 1]),
+                             a.z + round_bf16(v[4 * j + 2]), a.w + round_bf16(v[4 * j + 3]));
+        else
+          c[j] = make_float4(a.x + v[4 * j], a.y + v[4 * j + 1], a.z + v[4 * j + 2], a.w + v[4 * j + 3]);
+      }
+      break;
+    }
+    case NSB_EPI_DGELU: {
+      if (p.c_bf16) {
+        const uint4* h = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.aux) + o);
+        uint4* c = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.C) + o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint4 u = h[j];
+          const float2 h0 = unpack_bf16x2(u.x), h1 = unpack_bf16x2(u.y), h2 = unpack_bf16x2(u.z),
+                       h3 = unpack_bf16x2(u.w);
+          c[j] = make_uint4(pack_bf16x2(round_bf16(v[8 * j]) * gelu_exact_grad(h0.x),
+                                        round_bf16(v[8 * j + 1]) * gelu_exact_grad(h0.y)),
+                            pack_bf16x2(round_bf16(v[8 * j + 2]) * gelu_exact_grad(h1.x),
+                                        round_bf16(v[8 * j + 3]) * gelu_exact_grad(h1.y)),
+                            pack_bf16x2(round_bf16(v[8 * j + 4]) * gelu_exact_grad(h2.x),
+                                        round_bf16(v[8 * j + 5]) * gelu_exact_grad(h2.y)),
+                            pack_bf16x2(round_bf16(v[8 * j + 6]) * gelu_exact_grad(h3.x),
+                                        round_bf16(v[8 * j + 7]) * gelu_exact_grad(h3.y)));
+        }
+      } else {
+        const float4* h = reinterpret_cast<const float4*>(static_cast<const float*>(p.aux) + o);
+        float4* c = reinterpret_cast<float4*>(static_cast<float*>(p.C) + o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 a = h[j];
+          c[j] = make_float4(v[4 * j] * gelu_exact_grad(a.x), v[4 * j + 1] * gelu_exact_grad(a.y),
+                             v[4 * j + 2] * gelu_exact_grad(a.z), v[4 * j + 3] * gelu_exact_grad(a.w));
+        }
+      }
+      break;
+    }
+    default:
+      break;
+  }
+}
+
+// ---- the kernel -------------------------------------------------------------------------------
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1)
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                   int K, int num_m, int num_n, int splits, int kb_per_split, EpiParams ep) {
+  constexpr int STAGES = stages_for(BN);
+  constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
+  constexpr uint32_t TMEM_COLS = 2 * BN;
+  constexpr uint32_t IDESC = ptx::umma_idesc_bf16(BM, BN, A_MN, B_MN);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * A_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES));
+  uint64_t* full = bars;
+  uint64_t* empty = bars + STAGES;
+  uint64_t* tfull = bars + 2 * STAGES;
+  uint64_t* tempty = bars + 2 * STAGES + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_kb = (K + BK - 1) / BK;
+  const int total_work = num_m * num_n * splits;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tma_a);
+    ptx::prefetch_tmap(&tma_b);
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full[s], 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull[s], 1);
+      ptx::mbar_init(&tempty[s], 4);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================ TMA producer ==========================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int m_blk = w % num_m, rest = w / num_m;
+        const int n_blk = rest % num_n, split = rest / num_n;
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(total_kb, kb0 + kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          ptx::mbar_wait(&empty[stage], phase ^ 1);
+          ptx::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+          uint8_t* a_dst = smem_a + stage * A_BYTES;
+          uint8_t* b_dst = smem_b + stage * B_BYTES;
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              ptx::tma_load_2d(a_dst + j * (64 * BK * 2), &tma_a, &full[stage], m_blk * BM + j * 64, kb * BK);
+          } else {
+            ptx::tma_load_2d(a_dst, &tma_a, &full[stage], kb * BK, m_blk * BM);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              ptx::tma_load_2d(b_dst + j * (64 * BK * 2), &tma_b, &full[stage], n_blk * BN + j * 64, kb * BK);
+          } else {
+            ptx::tma_load_2d(b_dst, &tma_b, &full[stage], kb * BK, n_blk * BN);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ============================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int split = (w / num_m) / num_n;
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(total_kb, kb0 + kb_per_split);
+        ptx::mbar_wait(&tempty[as], aphase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(as * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          ptx::mbar_wait(&full[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t a_addr = ptx::smem_u32(smem_a + stage * A_BYTES);
+          const uint32_t b_addr = ptx::smem_u32(smem_b + stage * B_BYTES);
+          // K-major:  rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused (1).
+          // MN-major: [k][64 mn] boxes of 8 KB: LBO = next 64-wide mn block, SBO = next 8 k rows.
+          const uint64_t a_desc = A_MN ? ptx::umma_smem_desc_sw128(a_addr, 64 * BK * 2, 1024)
+                                       : ptx::umma_smem_desc_sw128(a_addr, 16, 1024);
+          const uint64_t b_desc = B_MN ? ptx::umma_smem_desc_sw128(b_addr, 64 * BK * 2, 1024)
+                                       : ptx::umma_smem_desc_sw128(b_addr, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t a_k = a_desc + static_cast<uint64_t>(A_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
+            const uint64_t b_k = b_desc + static_cast<uint64_t>(B_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
+            ptx::umma_bf16(d_tmem, a_k, b_k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        ptx::umma_commit(&tfull[as]);       // accumulator complete -> epilogue
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ================================ epilogue ==============================================
+    const int q = warp & 3;  // TMEM lane quarter this warp may touch
+    const float alpha = ep.alpha ? *ep.alpha : 1.f;
+    const bool use_atomics = (ep.kind == NSB_EPI_ACCUM) && splits > 1;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      const int m_blk = w % num_m, n_blk = (w / num_m) % num_n;
+      ptx::mbar_wait(&tfull[as], aphase);
+      ptx::tc_fence_after();
+      const int m = m_blk * BM + q * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        float v[32];
+        ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN + c * 32), v);
+        epilogue_row32(ep, m, n_blk * BN + c * 32, v, alpha, use_atomics);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty[as]);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---- host: tensor maps --------------------------------------------------------------------------
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr; uint64_t d0, d1, stride; uint32_t b0, b1;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && stride == o.stride && b0 == o.b0 && b1 == o.b1;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.ptr);
+    auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
+    mix(k.d0); mix(k.d1); mix(k.stride); mix(k.b0); mix(k.b1);
+    return h;
+  }
+};
+std::mutex g_map_mu;
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+}  // namespace
+
+// 2-D bf16 tensor [d1 rows][d0 contiguous], row stride in elements, box {b0, b1}, 128B swizzle
+int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t row_stride,
+                      uint32_t b0, uint32_t b1) {
+  MapKey key{ptr, d0, d1, row_stride, b0, b1};
+  {
+    std::lock_guard<std::mutex> g(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return 0; }
+  }
+  EncodeTiledFn fn = get_encode_fn();
+  NSB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+  NSB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (row_stride * 2) % 16 == 0,
+              "gemm: bf16 operand must be 16-byte aligned with a row stride multiple of 8 elements (stride %llu)",
+              static_cast<unsigned long long>(row_stride));
+  cuuint64_t gdim[2] = {d0, d1};
+  cuuint64_t gstr[1] = {row_stride * 2};
+  cuuint32_t box[2] = {b0, b1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  NSB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (dims %llu x %llu, stride %llu)",
+              static_cast<int>(r), static_cast<unsigned long long>(d0), static_cast<unsigned long long>(d1),
+              static_cast<unsigned long long>(row_stride));
+  std::lock_guard<std::mutex> g(g_map_mu);
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps.emplace(key, *out);
+  return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, int K, int num_m, int num_n, int splits,
+                          int kb_per_split, const EpiParams& ep, cudaStream_t stream) {
+  auto kern = gemm_tc_kernel<BN, A_MN, B_MN>;
+  static bool attr_done = false;
+  const size_t smem = smem_bytes_for(BN);
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    NSB_REQUIRE(e == cudaSuccess, "gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    attr_done = true;
+  }
+  const int total = num_m * num_n * splits;
+  const int grid = total < sm_count() ? total : sm_count();
+  kern<<<grid, kThreads, smem, stream>>>(ta, tb, K, num_m, num_n, splits, kb_per_split, ep);
+  count_launch();
+  return check_launch("gemm_tc");
+}
+
+int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t stream, int force_bn, int force_splits) {
+  const int M = a->M, N = a->N, K = a->K;
+  int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
+  if (force_bn == 128 || force_bn == 256) bn = force_bn;
+  const int num_m = (M + BM - 1) / BM, num_n = (N + bn - 1) / bn;
+  const int total_kb = (K + BK - 1) / BK;
+  // split-K only where the epilogue can accumulate atomically into a pre-existing fp32 C
+  int splits = 1;
+  if (ep.kind == NSB_EPI_ACCUM && ep.accumulate) {
+    const int tiles = num_m * num_n, sms = sm_count();
+    if (tiles < sms) {
+      splits = (2 * sms + tiles - 1) / tiles;
+      const int max_splits = total_kb / 8 > 0 ? total_kb / 8 : 1;  // keep >= 8 k-blocks per split
+      if (splits > max_splits) splits = max_splits;
+    }
+    if (force_splits > 0) splits = force_splits;
+  }
+  int kb_per_split = (total_kb + splits - 1) / splits;
+  if (kb_per_split < 1) kb_per_split = 1;
+  splits = (total_kb + kb_per_split - 1) / kb_per_split;
+  if (splits < 1) splits = 1;
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (a->a_kmajor) rc = make_tmap_bf16_2d(&ta, a->A, K, M, a->lda, BK, BM);
+  else             rc = make_tmap_bf16_2d(&ta, a->A, M, K, a->lda, 64, BK);
+  if (rc) return rc;
+  if (a->b_kmajor) rc = make_tmap_bf16_2d(&tb, a->B, K, N, a->ldb, BK, bn);
+  else             rc = make_tmap_bf16_2d(&tb, a->B, N, K, a->ldb, 64, BK);
+  if (rc) return rc;
+
+#define NSB_GEMM_CASE(BNV, AMN, BMN) \
+  return launch_variant<BNV, AMN, BMN>(ta, tb, K, num_m, num_n, splits, kb_per_split, ep, stream)
+  const bool amn = !a->a_kmajor, bmn = !a->b_kmajor;
+  if (bn == 256) {
+    if (!amn && !bmn) NSB_GEMM_CASE(256, false, false);
+    if (!amn && bmn) NSB_GEMM_CASE(256, false, true);
+    if (amn && !bmn) NSB_GEMM_CASE(256, true, false);
+    NSB_GEMM_CASE(256, true, true);
+  } else {
+    if (!amn && !bmn) NSB_GEMM_CASE(128, false, false);
+    if (!amn && bmn) NSB_GEMM_CASE(128, false, true);
+    if (amn && !bmn) NSB_GEMM_CASE(128, true, false);
+    NSB_GEMM_CASE(128, true, true);
+  }
+#undef NSB_GEMM_CASE
+}
+
+int gemm_simt_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t stream);
+
+}  // namespace nsb
+
+using namespace nsb;
+
+static int g_force_bn = 0, g_force_splits = 0, g_force_simt = 0;
+
+extern "C" {
+
+// test/tuning hooks (not part of the reference-facing surface): force the N tile, the split-K
+// factor, or route bf16 GEMMs through the SIMT kernel (debug cross-check).
+void nsb_gemm_debug_config(int force_bn, int force_splits, int force_simt) {
+  g_force_bn = force_bn;
+  g_force_splits = force_splits;
+  g_force_simt = force_simt;
+}
+
+int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
+  NSB_REQUIRE(a != nullptr, "gemm: null args");
+  NSB_REQUIRE(a->M >= 0 && a->N >= 0 && a->K >= 1, "gemm: bad shape %d x %d x %d", a->M, a->N, a->K);
+  NSB_REQUIRE(a->in_dtype == NSB_F32 || a->in_dtype == NSB_BF16, "gemm: bad in_dtype %d", a->in_dtype);
+  NSB_REQUIRE(a->epilogue >= NSB_EPI_STORE && a->epilogue <= NSB_EPI_DGELU, "gemm: bad epilogue %d", a->epilogue);
+  NSB_REQUIRE(a->A && a->B && a->C, "gemm: null operand");
+  NSB_REQUIRE(a->epilogue != NSB_EPI_GELU || a->C2, "gemm: GELU epilogue needs C2");
+  NSB_REQUIRE((a->epilogue != NSB_EPI_RESIDUAL && a->epilogue != NSB_EPI_DGELU) || a->aux, "gemm: epilogue needs aux");
+  if (a->M == 0 || a->N == 0) return 0;
+  EpiParams ep;
+  ep.kind = a->epilogue; ep.M = a->M; ep.N = a->N; ep.C = a->C; ep.C2 = a->C2; ep.aux = a->aux;
+  ep.bias = a->bias; ep.alpha = a->alpha; ep.ldc = a->ldc; ep.c_bf16 = (a->c_dtype == NSB_BF16) ? 1 : 0;
+  ep.accumulate = a->accumulate;
+  if (a->in_dtype == NSB_F32 || g_force_simt) return gemm_simt_launch(a, ep, cs(stream));
+  return gemm_tc_launch(a, ep, cs(stream), g_force_bn, g_force_splits);
+}
+
+}  // extern "C"

@@ -1,0 +1,315 @@
+"""Kernel-level parity (GPU): every C-ABI entry point against the stock torch op it replaces,
+called through the C-ABI (ctypes) on seeded inputs.  fp32 kernels: 1e-5 relative; bf16: 2e-2."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+if not torch.cuda.is_available():
+    pytest.skip("needs a GPU", allow_module_level=True)
+
+from nanosandbox_b200 import _lib, ops  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel_err(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-30)).item()
+
+
+def assert_close(a, b, rtol, what=""):
+    e = rel_err(a, b)
+    assert e < rtol and torch.isfinite(a.float()).all(), f"{what}: rel err {e:.3e} >= {rtol}"
+
+
+# ------------------------------------------------------------------------------------------------
+def test_embedding_fwd_bit_exact_and_bwd():
+    torch.manual_seed(0)
+    B, T, Cc, V = 3, 40, 128, 65
+    wte = torch.randn(V, Cc, device=DEV)
+    wpe = torch.randn(T, Cc, device=DEV)
+    idx = torch.randint(0, V, (B, T), device=DEV)
+    out = torch.empty(B, T, Cc, device=DEV)
+    ops.embedding_fwd(idx, wte, wpe, out)
+    ref = F.embedding(idx, wte) + F.embedding(torch.arange(T, device=DEV), wpe)
+    assert torch.equal(out, ref)  # bit-exact (north_star)
+    dx = torch.randn(B, T, Cc, device=DEV)
+    dwte = torch.randn(V, Cc, device=DEV)
+    dwpe = torch.randn(T, Cc, device=DEV)
+    rwte = dwte.clone().index_add_(0, idx.view(-1), dx.view(-1, Cc))
+    rwpe0 = dx.sum(0)
+    rwpe1 = dwpe + dx.sum(0)
+    d0 = dwpe.clone()
+    ops.embedding_bwd(idx, dx, dwte, d0, False)
+    assert_close(dwte, rwte, 1e-5, "dwte")
+    assert_close(d0, rwpe0, 1e-5, "dwpe")
+    d1 = dwpe.clone()
+    ops.embedding_bwd(idx, dx, dwte.clone(), d1, True)
+    assert_close(d1, rwpe1, 1e-5, "dwpe acc")
+
+
+@pytest.mark.parametrize("Cc", [64, 128, 384, 768, 1024])
+@pytest.mark.parametrize("bias", [False, True])
+@pytest.mark.parametrize("lowp", [False, True])
+def test_layernorm_fwd_bwd(Cc, bias, lowp):
+    torch.manual_seed(1)
+    M = 517
+    x = torch.randn(M, Cc, device=DEV) * 2 + 0.5
+    w = torch.randn(Cc, device=DEV)
+    b = torch.randn(Cc, device=DEV) if bias else None
+    ydt = torch.bfloat16 if lowp else torch.float32
+    y = torch.empty(M, Cc, device=DEV, dtype=ydt)
+    mean = torch.empty(M, device=DEV)
+    rstd = torch.empty(M, device=DEV)
+    ops.layernorm_fwd(x, w, b, y, mean, rstd)
+    xr = x.clone().requires_grad_(True)
+    wr = w.clone().requires_grad_(True)
+    br = b.clone().requires_grad_(True) if bias else None
+    ref = F.layer_norm(xr, (Cc,), wr, br, 1e-5)
+    assert_close(y, ref, 4e-3 if lowp else 1e-5, "ln fwd")
+    assert_close(mean, x.mean(-1), 1e-5, "mean")
+    dy = torch.randn(M, Cc, device=DEV).to(ydt)
+    dres = torch.randn(M, Cc, device=DEV)
+    ref.backward(dy.float())
+    dx = torch.empty(M, Cc, device=DEV)
+    dxl = torch.empty(M, Cc, device=DEV, dtype=torch.bfloat16) if lowp else None
+    dw = torch.full((Cc,), 3.0, device=DEV)
+    db = torch.full((Cc,), -2.0, device=DEV) if bias else None
+    scratch = torch.empty(ops.layernorm_bwd_scratch_bytes(M, Cc) // 4, device=DEV)
+    ops.layernorm_bwd(dy, x, w, mean, rstd, dres, dx, dxl, dw, db, True, scratch)
+    assert_close(dx, xr.grad + dres, 1e-5, "ln dx")
+    assert_close(dw, wr.grad + 3.0, 2e-5, "ln dw")
+    if bias:
+        assert_close(db, br.grad - 2.0, 2e-5, "ln db")
+    if lowp:
+        assert_close(dxl, dx, 4e-3, "ln dx lowp")
+    # no incoming residual, overwrite mode
+    ops.layernorm_bwd(dy, x, w, mean, rstd, None, dx, None, dw, db, False, scratch)
+    assert_close(dx, xr.grad, 1e-5, "ln dx no res")
+    assert_close(dw, wr.grad, 2e-5, "ln dw overwrite")
+
+
+@pytest.mark.parametrize("V,ld", [(65, 65), (65, 72), (1000, 1000), (50304, 50304), (50257, 50264)])
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_cross_entropy(V, ld, dt):
+    torch.manual_seed(2)
+    M = 257
+    store = (torch.randn(M, ld, device=DEV) * 3).to(dt)
+    logits = store[:, :V]
+    targets = torch.randint(0, V, (M,), device=DEV)
+    targets[5] = -1
+    targets[100] = -1
+    lse = torch.empty(M, device=DEV)
+    rl = torch.empty(M, device=DEV)
+    stats = torch.empty(2, device=DEV)
+    ops.cross_entropy_fwd(store, targets, lse, rl, stats, V)
+    lr = logits.float().clone().requires_grad_(True)
+    ref = F.cross_entropy(lr, targets, ignore_index=-1)
+    tol = 1e-5 if dt == torch.float32 else 1e-4
+    assert abs(stats[0].item() - ref.item()) < tol * max(1.0, abs(ref.item())), (stats, ref)
+    assert stats[1].item() == M - 2
+    assert_close(lse, torch.logsumexp(logits.float(), -1), 1e-5, "lse")
+    gs = torch.tensor([0.25], device=DEV)
+    (ref * 0.25).backward()
+    ops.cross_entropy_bwd(store, targets, lse, stats, gs, V)
+    assert_close(store[:, :V], lr.grad, 1e-5 if dt == torch.float32 else 6e-3, "dlogits")
+    if ld > V:
+        assert (store[:, V:] == 0).all()
+    assert (store[5] == 0).all() and (store[100] == 0).all()
+
+
+def test_grad_norm_and_adamw_match_torch():
+    torch.manual_seed(3)
+    n = 1024 * 37
+    n_decay = 1024 * 30
+    p = torch.randn(n, device=DEV)
+    flags = torch.zeros(n // 1024, dtype=torch.uint8, device=DEV)
+    flags[: n_decay // 1024] = 1
+    pd = p[:n_decay].clone().requires_grad_(True)
+    pn = p[n_decay:].clone().requires_grad_(True)
+    opt = torch.optim.AdamW([{"params": [pd], "weight_decay": 0.1}, {"params": [pn], "weight_decay": 0.0}],
+                            lr=6e-4, betas=(0.9, 0.95))
+    m = torch.zeros(n, device=DEV)
+    v = torch.zeros(n, device=DEV)
+    lowp = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    scratch = torch.empty(ops.grad_norm_scratch_bytes(n) // 4, device=DEV)
+    out = torch.empty(2, device=DEV)
+    for step in range(1, 6):
+        g = torch.randn(n, device=DEV) * (0.01 if step % 2 else 1.0)
+        pd.grad = g[:n_decay].clone()
+        pn.grad = g[n_decay:].clone()
+        tn = torch.nn.utils.clip_grad_norm_([pd, pn], 1.0)
+        opt.step()
+        ops.grad_clip_coef(g, 1.0, scratch, out)
+        assert abs(out[0].item() - tn.item()) < 1e-5 * tn.item()
+        lr, b1, b2 = 6e-4, 0.9, 0.95
+        bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step
+        ops.adamw_step(p, g, m, v, lowp, flags, b1, b2, 1e-8, 1 - lr * 0.1, lr / bc1, math.sqrt(bc2), out[1:])
+        ref = torch.cat([pd.detach(), pn.detach()])
+        assert_close(p, ref, 1e-6, f"adamw step {step}")
+        assert_close(lowp, ref, 4e-3, "bf16 shadow")
+
+
+def test_casts_and_colsum():
+    torch.manual_seed(4)
+    x = torch.randn(100003, device=DEV)
+    y = torch.empty(100003, device=DEV, dtype=torch.bfloat16)
+    ops.cast_f32_to_bf16(x, y, 0.5)
+    assert torch.equal(y, (x * 0.5).to(torch.bfloat16))
+    z = torch.empty(100003, device=DEV)
+    ops.cast_bf16_to_f32(y, z)
+    assert torch.equal(z, y.float())
+    w = x.clone()
+    ops.scale_f32(w, 0.125)
+    assert torch.equal(w, x * 0.125)
+    dy = torch.randn(300, 70, device=DEV)
+    db = torch.ones(70, device=DEV)
+    ops.colsum(dy, db, True)
+    assert_close(db, dy.sum(0) + 1, 1e-5, "colsum")
+
+
+# ------------------------------------------------------------------------------------------------
+def _gemm_case(dt, M, N, K, a_k, b_k, epi, seed=0, bias=False, accumulate=False, alpha=None):
+    torch.manual_seed(seed)
+    A = (torch.randn(M, K, device=DEV) / math.sqrt(K)).to(dt)
+    Bm = torch.randn(N, K, device=DEV).to(dt)
+    def mn_store(X):  # [K, rows] storage with the row stride padded to 8 elements (TMA: 16 B)
+        rows = X.shape[0]
+        st = torch.zeros(X.shape[1], (rows + 7) // 8 * 8, device=DEV, dtype=dt)
+        st[:, :rows] = X.t()
+        return st
+    A_st = A if a_k else mn_store(A)
+    B_st = Bm if b_k else mn_store(Bm)
+    acc = A.float() @ Bm.float().t()
+    al = None
+    if alpha is not None:
+        al = torch.tensor([alpha], device=DEV)
+        acc = acc * alpha
+    bv = torch.randn(N, device=DEV) if bias else None
+    lowp = dt == torch.bfloat16
+    rnd = (lambda t: t.to(torch.bfloat16).float()) if lowp else (lambda t: t)
+    cdt = dt
+    C2 = aux = None
+    if epi == _lib.EPI_STORE:
+        ref = rnd(acc + (bv if bias else 0))
+        Cout = torch.empty(M, N, device=DEV, dtype=cdt)
+    elif epi == _lib.EPI_GELU:
+        h = rnd(acc + (bv if bias else 0))
+        ref = (h, rnd(F.gelu(h)))
+        Cout = torch.empty(M, N, device=DEV, dtype=cdt)
+        C2 = torch.empty(M, N, device=DEV, dtype=cdt)
+    elif epi == _lib.EPI_RESIDUAL:
+        aux = torch.randn(M, N, device=DEV)
+        ref = aux + rnd(acc + (bv if bias else 0))
+        Cout = torch.empty(M, N, device=DEV)
+    elif epi == _lib.EPI_ACCUM:
+        Cout = torch.randn(M, N, device=DEV)
+        ref = (Cout.clone() if accumulate else 0) + acc
+    else:
+        aux = (torch.randn(M, N, device=DEV)).to(cdt)
+        hx = aux.float().clone().requires_grad_(True)
+        F.gelu(hx).backward(rnd(acc))
+        ref = rnd(hx.grad)
+        Cout = torch.empty(M, N, device=DEV, dtype=cdt)
+    ops.gemm(M, N, K, A_st, A_st.stride(0), a_k, B_st, B_st.stride(0), b_k, Cout, Cout.stride(0), epi,
+             C2=C2, aux=aux, bias=bv, alpha=al, accumulate=accumulate)
+    torch.cuda.synchronize()
+    tol = 1e-2 if lowp else 2e-5
+    if epi == _lib.EPI_GELU:
+        assert_close(Cout, ref[0], tol, "gelu pre")
+        assert_close(C2, ref[1], tol, "gelu out")
+    else:
+        assert_close(Cout, ref, tol, f"gemm epi {epi}")
+
+
+SHAPES = [(128, 128, 64), (256, 256, 128), (300, 200, 136), (1024, 768, 768), (512, 65, 384), (384, 1152, 1024)]
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_kmajor_store(dt, M, N, K):
+    _gemm_case(dt, M, N, K, True, True, _lib.EPI_STORE)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("a_k,b_k", [(True, False), (False, True), (False, False)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (384, 640, 1024), (768, 2304, 2048)])
+def test_gemm_mn_major(dt, a_k, b_k, M, N, K):
+    _gemm_case(dt, M, N, K, a_k, b_k, _lib.EPI_STORE)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("epi", [_lib.EPI_GELU, _lib.EPI_RESIDUAL, _lib.EPI_DGELU])
+@pytest.mark.parametrize("bias", [False, True])
+def test_gemm_epilogues(dt, epi, bias):
+    _gemm_case(dt, 640, 768, 256, True, True, epi, bias=bias and epi != _lib.EPI_DGELU, alpha=0.5 if epi == _lib.EPI_DGELU else None)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("accumulate", [False, True])
+@pytest.mark.parametrize("M,N,K", [(768, 768, 4096), (2304, 768, 2048), (65, 384, 1024), (200, 120, 520)])
+def test_gemm_wgrad_accum(dt, accumulate, M, N, K):
+    # weight-gradient form: both operands MN-major, fp32 accumulate output (split-K when accumulating)
+    _gemm_case(dt, M, N, K, False, False, _lib.EPI_ACCUM, accumulate=accumulate, alpha=0.125)
+
+
+def test_gemm_tc_matches_simt_path():
+    """The tcgen05 kernel against our own exact SIMT kernel on identical bf16 inputs."""
+    torch.manual_seed(7)
+    M, N, K = 512, 512, 512
+    A = torch.randn(M, K, device=DEV).to(torch.bfloat16)
+    Bm = torch.randn(N, K, device=DEV).to(torch.bfloat16)
+    c1 = torch.empty(M, N, device=DEV)
+    c2 = torch.empty(M, N, device=DEV)
+    lib = _lib.load()
+    ops.gemm(M, N, K, A, K, True, Bm, K, True, c1, N)
+    lib.nsb_gemm_debug_config(0, 0, 1)
+    try:
+        ops.gemm(M, N, K, A, K, True, Bm, K, True, c2, N)
+    finally:
+        lib.nsb_gemm_debug_config(0, 0, 0)
+    torch.cuda.synchronize()
+    assert_close(c1, c2, 1e-5, "tc vs simt")
+
+
+# ------------------------------------------------------------------------------------------------
+def _attention_ref(qkv, B, T, H, D):
+    Cc = H * D
+    q, k, v = qkv.split(Cc, dim=2)
+    q = q.view(B, T, H, D).transpose(1, 2)
+    k = k.view(B, T, H, D).transpose(1, 2)
+    v = v.view(B, T, H, D).transpose(1, 2)
+    y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    return y.transpose(1, 2).contiguous().view(B, T, Cc)
+
+
+@pytest.mark.parametrize("dt,B,T,H,D", [
+    (torch.float32, 2, 64, 4, 32), (torch.float32, 2, 100, 2, 64),
+    (torch.bfloat16, 2, 256, 6, 64), (torch.bfloat16, 1, 1024, 2, 64), (torch.bfloat16, 3, 100, 2, 64),
+    (torch.bfloat16, 2, 64, 4, 32)])
+def test_attention_fwd_bwd(dt, B, T, H, D):
+    torch.manual_seed(5)
+    Cc = H * D
+    qkv = (torch.randn(B, T, 3 * Cc, device=DEV)).to(dt)
+    dy = torch.randn(B, T, Cc, device=DEV).to(dt)
+    y = torch.empty(B, T, Cc, device=DEV, dtype=dt)
+    lse = torch.empty(B, H, T, device=DEV)
+    ops.attention_fwd(qkv, y, lse, B, T, H, D)
+    ref_in = qkv.float().clone().requires_grad_(True)
+    ref = _attention_ref(ref_in, B, T, H, D)
+    tol = 1e-5 if dt == torch.float32 else 1e-2
+    assert_close(y, ref, tol, "attn fwd")
+    ref.backward(dy.float())
+    dqkv = torch.zeros_like(qkv)
+    delta = torch.empty(B, H, T, device=DEV)
+    ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D)
+    torch.cuda.synchronize()
+    g = ref_in.grad
+    btol = 2e-5 if dt == torch.float32 else 2e-2
+    assert_close(dqkv[..., :Cc], g[..., :Cc], btol, "dq")
+    assert_close(dqkv[..., Cc:2 * Cc], g[..., Cc:2 * Cc], btol, "dk")
+    assert_close(dqkv[..., 2 * Cc:], g[..., 2 * Cc:], btol, "dv")
