@@ -1,0 +1,320 @@
+"""Headline benchmark: GPT-2 124M data-parallel training throughput (tokens/s, MFU) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # our arm (CUDA kernels)
+    python bench.py --impl reference [--gpus N] --steps K --warmup W  # the CPU restatement, host cores
+
+A "step" is one optimizer step of BASELINE.json's headline configuration (cfg4): batch 12 x block
+1024 x 40 accumulation micro-steps = 491,520 tokens, split evenly over the ranks (40/N micro-steps
+each), synthetic uniform tokens over the 50304 vocabulary, random-init weights, bf16 autocast
+policy, grad clip 1.0, AdamW.  Under torchrun (N>1) one rank per GPU, our bucketed NCCL all-reduce.
+Prints ONE JSON line on rank 0 (keys: see the bench contract in DESIGN.md section 6).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG = dict(n_layer=12, n_head=12, n_embd=768, block_size=1024, vocab_size=50304, bias=False, dropout=0.0)
+BATCH, ACCUM_TOTAL = 12, 40
+WORKLOAD = "gpt2-124M (12L/12H/768, block 1024, vocab 50304) batch 12 x accum 40 = 491520 tokens/step, bf16 [BASELINE.json configs[3]]"
+FLOPS_PER_TOKEN = 854_770_176  # 6N + 12LHQT, SURVEY.md 8d
+NOMINAL_BF16 = 2.25e15
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf=d["bf16_tflops"], tf_sus=d.get("bf16_tflops_sustained", d["bf16_tflops"]), src="measured")
+    return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_run(steps: int, warmup: int, micro_batch: int = 2):
+    """The reference's CPU path (oracle restatement, stock torch ops) on all host cores, on a
+    bounded sample of the workload: one micro-step of `micro_batch` x 1024 tokens per step."""
+    from oracle.model import GPT as RefGPT, GPTConfig as RefConfig
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(1337)
+    model = RefGPT(RefConfig(**CFG), verbose=False)
+    opt = model.configure_optimizers(0.1, 6e-4, (0.9, 0.95), "cpu", verbose=False)
+    g = torch.Generator().manual_seed(0)
+    toks = torch.randint(0, CFG["vocab_size"], (1 << 20,), generator=g)
+    T = CFG["block_size"]
+
+    def one():
+        ix = torch.randint(len(toks) - T - 1, (micro_batch,))
+        x = torch.stack([toks[i:i + T] for i in ix])
+        y = torch.stack([toks[i + 1:i + 1 + T] for i in ix])
+        _, loss = model(x, y)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        return float(loss)
+
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = time.perf_counter() - t0
+    tok_s = steps * micro_batch * T / dt
+    sample = (f"{steps} optimizer steps of one {micro_batch}x{T}-token micro-step (fwd+bwd+clip+AdamW), fp32, "
+              f"oracle/ restatement on stock torch CPU ops, {cores} threads; the full step is 240x this sample")
+    return tok_s, dt / steps * 1e3, cores, sample
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 3))
+    warm = 1 if args.warmup > 0 else 0
+    tok_s, ms, cores, sample = cpu_reference_run(steps, warm)
+    line = {"impl": "reference", "metric": "train_tokens_per_sec", "value": tok_s, "unit": "tokens/s",
+            "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD},
+            "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": tok_s, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bucket-dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
+                         "(use --impl reference for the CPU restatement)")
+    args.warmup = max(args.warmup, 3)
+
+    import torch.distributed as dist
+    from nanosandbox_b200 import ops
+    from nanosandbox_b200.data import uniform_stream
+    from nanosandbox_b200.ddp import DistributedDataParallel as DDP
+    from nanosandbox_b200.model import GPT, GPTConfig
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    ddp = world > 1
+    if ddp:
+        dist.init_process_group(backend="nccl", device_id=dev)
+    assert ACCUM_TOTAL % world == 0
+    accum = ACCUM_TOTAL // world
+    T, V = CFG["block_size"], CFG["vocab_size"]
+    tokens_per_step = ACCUM_TOTAL * BATCH * T
+
+    torch.manual_seed(1337 + rank)
+    model = GPT(GPTConfig(**CFG), verbose=False).to(dev)
+    opt = model.configure_optimizers(0.1, 6e-4, (0.9, 0.95), "cuda", verbose=False)
+    raw = model
+    if ddp:
+        model = DDP(model, device_ids=[local_rank], bucket_dtype=args.bucket_dtype)
+    data = uniform_stream(V, 1 << 22, seed=0)
+    ctx = torch.autocast("cuda", dtype=torch.bfloat16)
+
+    def host_batch():
+        ix = torch.randint(len(data) - T, (BATCH,))
+        x = torch.stack([torch.from_numpy(data[i:i + T].astype(np.int64)) for i in ix])
+        y = torch.stack([torch.from_numpy(data[i + 1:i + 1 + T].astype(np.int64)) for i in ix])
+        return x.pin_memory(), y.pin_memory()
+
+    def train_step(batches, from_host: bool):
+        """One optimizer step through the public API (GPT.forward / backward / clip / AdamW)."""
+        loss = None
+        for micro in range(accum):
+            if ddp:
+                model.require_backward_grad_sync = (micro == accum - 1)
+            if from_host:
+                xh, yh = host_batch()
+                X, Y = xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)
+            else:
+                X, Y = batches[micro]
+            with ctx:
+                _, loss = model(X, Y)
+                loss = loss / accum
+            loss.backward()
+        opt.clip_grad_norm_(1.0)
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        return loss
+
+    resident = [tuple(t.to(dev) for t in host_batch()) for _ in range(accum)]
+
+    def barrier():
+        if ddp:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if ddp:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item()
+
+    # ---- warm-up, then the device-resident timed region ("value") ----
+    for _ in range(args.warmup):
+        train_step(resident, False)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = ops.launch_count()
+    if ddp:
+        model.buckets.time_comm = False
+    ms = timed(lambda: train_step(resident, False), args.steps)
+    launches = ops.launch_count() - launches0
+    value = tokens_per_step * args.steps / (ms / 1e3)
+
+    # ---- end-to-end: host batches from pinned memory + loss read back every step ----
+    def e2e_step():
+        loss = train_step(None, True)
+        return loss.item()  # device -> host read of the step's result
+    e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e_value = tokens_per_step * args.steps / (ms_e2e / 1e3)
+    h2d = accum * world * 2 * BATCH * T * 8
+    d2h = 4 * world
+
+    # ---- roofline of the dominant kernel (tcgen05 GEMM): CUDA events around every GEMM launch
+    #      of one more step, on the launching stream ----
+    peaks = load_peaks()
+    ev = []
+    orig_gemm = ops.gemm
+
+    def timed_gemm(M, N, K, *a, **k):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        orig_gemm(M, N, K, *a, **k)
+        e.record()
+        ev.append((2.0 * M * N * K, s, e))
+    import nanosandbox_b200.model as model_mod
+    model_mod.ops.gemm = timed_gemm
+    try:
+        train_step(resident, False)
+        torch.cuda.synchronize()
+    finally:
+        model_mod.ops.gemm = orig_gemm
+    g_flops = sum(f for f, _, _ in ev)
+    g_ms = sum(s.elapsed_time(e) for _, s, e in ev)
+    achieved = g_flops / (g_ms / 1e3) / 1e12
+    roofline = {"kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA bf16 GEMM, all layouts/epilogues)", "bound": "tensor",
+                "achieved": achieved, "peak": peaks["tf_sus"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sus"],
+                "traffic": None, "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json bf16_tflops_sustained: kernel timed inside a long step)",
+                "launches_timed": len(ev), "avg_launch_us": g_ms * 1e3 / max(1, len(ev)),
+                "algorithmic_flops_per_launch": g_flops / max(1, len(ev)),
+                "gemm_share_of_step": g_ms / (ms / args.steps)}
+
+    # ---- all-reduce bus bandwidth (N > 1): events on the communication stream ----
+    comm = None
+    if ddp:
+        model.buckets.time_comm = True
+        model.buckets.comm_events = []
+        b0 = model.buckets.bytes_reduced
+        train_step(resident, False)
+        torch.cuda.synchronize()
+        t_ms = sum(a.elapsed_time(b) for a, b in model.buckets.comm_events)
+        nbytes = model.buckets.bytes_reduced - b0
+        t = torch.tensor([t_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        comm = {"bytes_per_rank_per_step": nbytes, "ms_on_comm_stream": t.item(),
+                "busbw_GBps": nbytes * 2 * (world - 1) / world / (t.item() / 1e3) / 1e9,
+                "nominal_GBps": 900.0, "bucket_dtype": args.bucket_dtype}
+        model.buckets.time_comm = False
+
+    if rank == 0:
+        cpu = None
+        if not args.no_cpu_baseline:
+            tok_s, _, cores, sample = cpu_reference_run(2, 1)
+            cpu = {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample}
+        line = {
+            "metric": "train_tokens_per_sec", "value": value, "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "parallelism": f"dp{world}", "micro_steps_per_rank": accum,
+                       "l2": "inputs larger than L2: every micro-step streams ~6 GB of activations/weights (126 MB L2)",
+                       "grad_allreduce": args.bucket_dtype if ddp else "none"},
+            "mfu": {"flops_per_token": FLOPS_PER_TOKEN,
+                    "vs_nominal_2.25PF": value * FLOPS_PER_TOKEN / (world * NOMINAL_BF16),
+                    "vs_measured_peak": value * FLOPS_PER_TOKEN / (world * peaks["tf"] * 1e12),
+                    "measured_peak_tflops": peaks["tf"]},
+            "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        }
+        if comm is not None:
+            line["allreduce"] = comm
+        print(json.dumps(line), flush=True)
+    if ddp:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

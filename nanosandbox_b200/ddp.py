@@ -1,0 +1,146 @@
+"""Data-parallel wrapper: our own gradient bucket manager in place of
+``torch.nn.parallel.DistributedDataParallel`` + the C++ Reducer
+(torch/nn/parallel/distributed.py:661-674, 801, 881-890; torch/include/torch/csrc/distributed/c10d/
+reducer.hpp) on the path ``train.py`` takes when RANK is set (/root/reference/README.md:6-8).
+
+Same contract as DDP for nanoGPT's loop: ``.module``,
+``.require_backward_grad_sync`` written every micro-step, ``__call__`` -> ``(logits, loss)``,
+rank-0 parameters broadcast at construction, and after the last micro-step's ``backward()``
+every ``.grad`` is the mean over ranks of the locally accumulated gradient.
+
+Differences by design: a bucket is a contiguous slice of the flat gradient arena (no copies in or
+out of bucket views); the 1/world scaling is fused into the pack kernel that casts the slice to
+bf16; the all-reduce runs over NCCL (NVLink 5 / NVSwitch) on a side stream as soon as backward has
+finalised that slice, overlapping the rest of backward.  ``bucket_dtype='fp32'`` keeps exact
+DDP numerics (scale in place, all-reduce the fp32 slice itself).
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import Callable, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+class GradBucketManager:
+    """Host logic of the bucketed all-reduce; kernels are injected so that the logic can be driven
+    on CPU/gloo in tests while the product path uses the CUDA pack/unpack kernels."""
+
+    def __init__(self, grads: torch.Tensor, ranges: List[Tuple[int, int]], world_size: int,
+                 process_group=None, bucket_dtype: str = "bf16",
+                 pack: Optional[Callable] = None, unpack: Optional[Callable] = None,
+                 scale: Optional[Callable] = None):
+        assert bucket_dtype in ("bf16", "fp32")
+        self.grads, self.ranges, self.world = grads, ranges, world_size
+        self.pg = process_group
+        self.bucket_dtype = bucket_dtype
+        self.pack, self.unpack, self.scale = pack, unpack, scale
+        self.cuda = grads.is_cuda
+        self.staging = (torch.empty(grads.numel(), dtype=torch.bfloat16, device=grads.device)
+                        if bucket_dtype == "bf16" else None)
+        self.comm_stream = torch.cuda.Stream(device=grads.device, priority=-1) if self.cuda else None
+        self.launched: List[int] = []
+        self.bytes_reduced = 0
+        self.comm_events: List[Tuple[object, object]] = []
+        self.time_comm = False
+
+    def reduce_bucket(self, k: int) -> None:
+        s, e = self.ranges[k]
+        g = self.grads[s:e]
+        inv = 1.0 / self.world
+        if self.cuda:
+            ev = torch.cuda.current_stream().record_event()
+            self.comm_stream.wait_event(ev)
+            ctx = torch.cuda.stream(self.comm_stream)
+        else:
+            ctx = contextlib.nullcontext()
+        with ctx:
+            t0 = t1 = None
+            if self.cuda and self.time_comm:
+                t0 = torch.cuda.Event(enable_timing=True)
+                t1 = torch.cuda.Event(enable_timing=True)
+                t0.record()
+            if self.bucket_dtype == "bf16":
+                st = self.staging[s:e]
+                self.pack(g, st, inv)                       # cast fp32 -> bf16 and scale by 1/world
+                dist.all_reduce(st, op=dist.ReduceOp.SUM, group=self.pg)
+                self.unpack(st, g)                          # bf16 -> fp32 back into the arena slice
+                self.bytes_reduced += st.numel() * 2
+            else:
+                self.scale(g, inv)                          # divide first, then sum: DDP's order
+                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.pg)
+                self.bytes_reduced += g.numel() * 4
+            if t0 is not None:
+                t1.record()
+                self.comm_events.append((t0, t1))
+        self.launched.append(k)
+
+    def finish(self) -> None:
+        """Fence: the compute stream waits for every bucket launched during this backward."""
+        if self.cuda:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        assert self.launched == list(range(len(self.ranges))), \
+            f"buckets reduced out of order or missing: {self.launched}"
+        self.launched = []
+
+
+class DistributedDataParallel:
+    def __init__(self, module, device_ids=None, process_group=None, bucket_dtype: str = "bf16",
+                 broadcast_parameters: bool = True):
+        from . import ops
+        self.module = module
+        self.require_backward_grad_sync = True
+        self.process_group = process_group
+        self.world_size = dist.get_world_size(process_group)
+        arena = module.arena()
+        if broadcast_parameters:
+            # one broadcast over the flat parameter arena (DDP: _sync_module_states, 250 MiB chunks)
+            dist.broadcast(arena.params, src=0, group=process_group)
+            arena.lowp_version = -1
+        self.buckets = GradBucketManager(
+            arena.grads, module.bucket_ranges, self.world_size, process_group, bucket_dtype,
+            pack=lambda g, st, inv: ops.cast_f32_to_bf16(g, st, inv),
+            unpack=lambda st, g: ops.cast_bf16_to_f32(st, g),
+            scale=lambda g, inv: ops.scale_f32(g, inv))
+        module._grad_sync = self
+
+    # hooks called by GPT._engine_backward on the compute stream
+    def bucket_ready(self, k: int) -> None:
+        if self.require_backward_grad_sync:
+            self.buckets.reduce_bucket(k)
+
+    def finish_backward(self) -> None:
+        if self.require_backward_grad_sync:
+            self.buckets.finish()
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def __call__(self, *a, **k):
+        return self.module(*a, **k)
+
+    forward = __call__
+
+    def parameters(self, *a, **k):
+        return self.module.parameters(*a, **k)
+
+    def named_parameters(self, *a, **k):
+        return self.module.named_parameters(*a, **k)
+
+    def state_dict(self, *a, **k):
+        return {"module." + kk: v for kk, v in self.module.state_dict(*a, **k).items()}
+
+    def train(self, mode=True):
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        self.module.eval()
+        return self

@@ -1,0 +1,148 @@
+"""Model-level parity (GPU): nanosandbox_b200.GPT against the oracle on the same seed and inputs.
+fp32: logits / loss / gradients within 1e-5 relative; bf16 autocast: 2e-2 (north_star)."""
+import copy
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+if not torch.cuda.is_available():
+    pytest.skip("needs a GPU", allow_module_level=True)
+
+from nanosandbox_b200.model import GPT, GPTConfig  # noqa: E402
+from oracle.model import GPT as RefGPT, GPTConfig as RefConfig  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-30)).item()
+
+
+def build_pair(bias, **kw):
+    torch.manual_seed(1337)
+    ref = RefGPT(RefConfig(bias=bias, dropout=0.0, **kw), verbose=False)
+    rng_after_ref = torch.get_rng_state()
+    torch.manual_seed(1337)
+    ours = GPT(GPTConfig(bias=bias, dropout=0.0, **kw), verbose=False)
+    # same constructors in the same order -> same RNG consumption (get_batch parity depends on it)
+    assert torch.equal(torch.get_rng_state(), rng_after_ref)
+    for (n1, p1), (n2, p2) in zip(ref.named_parameters(), ours.named_parameters()):
+        assert n1 == n2 and torch.equal(p1, p2)
+    assert list(ref.state_dict().keys()) == list(ours.state_dict().keys())
+    return ref, ours
+
+
+CASES = [
+    dict(n_layer=2, n_head=2, n_embd=64, block_size=32, vocab_size=65),       # notebook smoke shape (D=32)
+    dict(n_layer=4, n_head=4, n_embd=128, block_size=64, vocab_size=65),      # cfg1
+    dict(n_layer=2, n_head=6, n_embd=384, block_size=256, vocab_size=65),     # cfg2 width, 2 layers
+    dict(n_layer=2, n_head=4, n_embd=256, block_size=128, vocab_size=1000),
+]
+
+
+@pytest.mark.parametrize("case", range(len(CASES)))
+@pytest.mark.parametrize("bias", [False, True])
+def test_fp32_forward_backward_matches_oracle(case, bias):
+    kw = CASES[case]
+    ref, ours = build_pair(bias, **kw)
+    if bias:  # make the biases non-trivial
+        with torch.no_grad():
+            for (_, p1), (_, p2) in zip(ref.named_parameters(), ours.named_parameters()):
+                if p1.dim() == 1:
+                    p1.add_(torch.randn_like(p1) * 0.05)
+                    p2.copy_(p1)
+    ref = ref.double()  # fp64 oracle: both fp32 implementations must sit within 1e-5 of it
+    ours.to(DEV)
+    B, T, V = 4, kw["block_size"], kw["vocab_size"]
+    g = torch.Generator().manual_seed(7)
+    idx = torch.randint(0, V, (B, T), generator=g)
+    tgt = torch.randint(0, V, (B, T), generator=g)
+    tgt[0, 3] = -1
+    rl, rloss = ref(idx, tgt)
+    (rloss / 4).backward()
+    ours.zero_grad()
+    ol, oloss = ours(idx.to(DEV), tgt.to(DEV))
+    assert ol.shape == rl.shape
+    assert rel(ol.cpu(), rl) < 1e-5
+    assert abs(oloss.item() - rloss.item()) < 1e-5 * abs(rloss.item())
+    (oloss / 4).backward()
+    torch.cuda.synchronize()
+    for (n1, p1), (n2, p2) in zip(ref.named_parameters(), ours.named_parameters()):
+        e = rel(p2.grad.cpu(), p1.grad)
+        assert e < 1e-5, f"{n1}: grad rel err {e:.2e}"
+    # accumulation: a second backward adds
+    g0 = {n: p.grad.clone() for n, p in ours.named_parameters()}
+    ol, oloss = ours(idx.to(DEV), tgt.to(DEV))
+    (oloss / 4).backward()
+    for n, p in ours.named_parameters():
+        assert rel(p.grad, 2 * g0[n]) < 1e-5, n
+
+
+@pytest.mark.parametrize("case", [2, 3])
+def test_bf16_forward_backward_matches_oracle(case):
+    kw = CASES[case]
+    ref, ours = build_pair(False, **kw)
+    ours.to(DEV)
+    ref.to(DEV)
+    B, T, V = 8, kw["block_size"], kw["vocab_size"]
+    g = torch.Generator().manual_seed(7)
+    idx = torch.randint(0, V, (B, T), generator=g).to(DEV)
+    tgt = torch.randint(0, V, (B, T), generator=g).to(DEV)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        rl, rloss = ref(idx, tgt)
+    rloss.backward()
+    ours.zero_grad()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        ol, oloss = ours(idx, tgt)
+    assert ol.dtype == torch.bfloat16
+    assert rel(ol, rl) < 2e-2
+    assert abs(oloss.item() - rloss.item()) < 2e-2 * abs(rloss.item())
+    oloss.backward()
+    torch.cuda.synchronize()
+    for (n1, p1), (n2, p2) in zip(ref.named_parameters(), ours.named_parameters()):
+        e = rel(p2.grad, p1.grad)
+        assert e < 2e-2, f"{n1}: grad rel err {e:.2e}"
+
+
+def test_inference_path_and_generate():
+    kw = CASES[1]
+    ref, ours = build_pair(False, **kw)
+    ours.to(DEV).eval()
+    ref.eval()
+    idx = torch.randint(0, 65, (3, 40))
+    with torch.no_grad():
+        rl, rloss = ref(idx)
+        ol, oloss = ours(idx.to(DEV))
+    assert oloss is None and ol.shape == (3, 1, 65)
+    assert rel(ol.cpu(), rl) < 1e-5
+    out = ours.generate(idx[:, :5].to(DEV), 8, top_k=10)
+    assert out.shape == (3, 13)
+
+
+def test_training_steps_match_oracle_fp32():
+    """Five optimizer steps (grad accumulation 2, clip, AdamW) against stock torch on the oracle."""
+    kw = CASES[1]
+    ref, ours = build_pair(False, **kw)
+    ours.to(DEV)
+    ropt = ref.configure_optimizers(0.1, 1e-3, (0.9, 0.95), "cpu", verbose=False)
+    oopt = ours.configure_optimizers(0.1, 1e-3, (0.9, 0.95), "cuda", verbose=False)
+    g = torch.Generator().manual_seed(11)
+    for step in range(5):
+        for micro in range(2):
+            idx = torch.randint(0, 65, (6, 64), generator=g)
+            tgt = torch.randint(0, 65, (6, 64), generator=g)
+            _, rloss = ref(idx, tgt)
+            (rloss / 2).backward()
+            _, oloss = ours(idx.to(DEV), tgt.to(DEV))
+            (oloss / 2).backward()
+            assert abs(oloss.item() - rloss.item()) < 2e-5 * abs(rloss.item()), (step, micro)
+        rn = torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+        on = oopt.clip_grad_norm_(1.0)
+        assert abs(on.item() - rn.item()) < 1e-4 * rn.item()
+        ropt.step(); ropt.zero_grad(set_to_none=True)
+        oopt.step(); oopt.zero_grad(set_to_none=True)
+    for (n1, p1), (n2, p2) in zip(ref.named_parameters(), ours.named_parameters()):
+        assert rel(p2.detach().cpu(), p1.detach()) < 1e-5, n1
