@@ -96,7 +96,7 @@ def cpu_reference_run(steps: int, warmup: int, micro_batch: int = 2):
         torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
         opt.step()
         opt.zero_grad(set_to_none=True)
-        return float(loss)
+        return float(loss.detach())
 
     for _ in range(warmup):
         one()
