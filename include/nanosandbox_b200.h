@@ -57,6 +57,22 @@ int nsb_layernorm_bwd(const void* dy, int dy_dtype, const float* x, const float*
                       void* dx_lowp, float* dw, float* db, int accumulate, float* scratch,
                       size_t scratch_bytes, int M, int C, nsb_stream_t stream);
 
+/* LayerNorm backward without caller scratch.  No counterpart in the reference: it exists for
+ * hosts that can pass inputs and outputs but cannot allocate device memory themselves -- an
+ * operator plugged into another runtime that only hands over its tensors, a caller inside a stream
+ * capture, a deployment with a fixed memory plan.  Same arguments and results as
+ * nsb_layernorm_bwd minus scratch/scratch_bytes: the partial sums go to a 1.16 MiB array built
+ * into the library (one copy per GPU that loads it, held until the process exits), so it serves
+ * rows of at most 1024 columns (any number of rows) and fails with a message beyond that.  It
+ * calls no cudaMalloc/cudaFree.  The first call on each device looks up the array's device address;
+ * make that call before starting any stream capture.  All calls on a device share the one array
+ * (nothing in it needs clearing between calls), therefore two calls that may run on the GPU at the
+ * same time -- different streams, no ordering between them -- race on it: keep them ordered. */
+int nsb_layernorm_bwd_noalloc(const void* dy, int dy_dtype, const float* x, const float* w,
+                              const float* mean, const float* rstd, const float* dres_in, float* dx,
+                              void* dx_lowp, float* dw, float* db, int accumulate, int M, int C,
+                              nsb_stream_t stream);
+
 /* K9: softmax cross-entropy with ignore_index=-1, mean over non-ignored rows.
  * Replaces F.cross_entropy (torch/nn/functional.py:3421).  logits [M, ld] (ld >= V), dtype f32
  * or bf16.  Writes lse[M], row_loss[M] and stats[0]=mean loss, stats[1]=#valid rows. */

@@ -43,6 +43,7 @@ SIGNATURES = {
     "nsb_layernorm_fwd": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _F, _P]),
     "nsb_layernorm_bwd_scratch_bytes": (_Z, [_I, _I]),
     "nsb_layernorm_bwd": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _Z, _I, _I, _P]),
+    "nsb_layernorm_bwd_noalloc": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "nsb_cross_entropy_fwd": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _P]),
     "nsb_cross_entropy_bwd": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _P]),
     "nsb_grad_norm_scratch_bytes": (_Z, [_Z]),

@@ -819,3 +819,66 @@ int nsb_colsum(const void* dy, int dtype, int ld, float* db, int accumulate, int
 }
 
 }  // extern "C"
+
+// =============================================================================================
+// LayerNorm backward for callers that cannot hand us scratch memory
+// =============================================================================================
+// Every other entry point of this library expects the caller to own all device memory, including
+// the partial-sum scratch of the LayerNorm backward.  Some hosts cannot provide that buffer: an
+// operator plugged into a foreign runtime only ever receives its input and output pointers, and a
+// caller that is in the middle of a stream capture, or that runs under a fixed memory plan, may
+// not call cudaMalloc at all.  For them the scratch lives in the library image itself: a
+// file-scope device array, present once on every GPU that loads the library until the process
+// exits.  Its size fixes the limit of this variant: rows up to kNoAllocMaxC wide.
+namespace nsb {
+constexpr int kNoAllocMaxC = 1024;     // widest row (n_embd) the built-in scratch can serve
+constexpr int kNoAllocMaxParts = 148;  // column-partial slabs kept: one per SM of a B200
+static __device__ __align__(256) float g_ln_bwd_builtin_scratch[kNoAllocMaxParts * 2 * kNoAllocMaxC];  // 1.16 MiB
+
+// In host code the array's name only stands for the symbol; the address a kernel can use has to be
+// asked for, per device, with that device current.
+constexpr int kMaxDevices = 64;
+static float* g_builtin_scratch_addr[kMaxDevices] = {nullptr};
+static std::atomic<int> g_builtin_scratch_lock{0};
+
+static int builtin_scratch_for_current_device(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    set_error("layernorm_bwd_noalloc: cannot identify the current device (%s)", cudaGetErrorString(e));
+    return e != cudaSuccess ? static_cast<int>(e) : -1;
+  }
+  while (g_builtin_scratch_lock.exchange(1, std::memory_order_acquire)) {}
+  float* p = g_builtin_scratch_addr[dev];
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_ln_bwd_builtin_scratch);
+    if (e != cudaSuccess) {
+      g_builtin_scratch_lock.store(0, std::memory_order_release);
+      set_error("layernorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return static_cast<int>(e);
+    }
+    g_builtin_scratch_addr[dev] = p;
+  }
+  g_builtin_scratch_lock.store(0, std::memory_order_release);
+  *out = p;
+  return 0;
+}
+}  // namespace nsb
+
+extern "C" int nsb_layernorm_bwd_noalloc(const void* dy, int dy_dtype, const float* x, const float* w,
+                                         const float* mean, const float* rstd, const float* dres_in,
+                                         float* dx, void* dx_lowp, float* dw, float* db, int accumulate,
+                                         int M, int C, nsb_stream_t stream) {
+  NSB_REQUIRE(C <= kNoAllocMaxC,
+              "layernorm_bwd_noalloc: row width %d exceeds the built-in scratch (at most %d columns); "
+              "use nsb_layernorm_bwd with caller-provided scratch",
+              C, kNoAllocMaxC);
+  NSB_REQUIRE(M >= 0, "layernorm_bwd_noalloc: negative row count %d", M);
+  float* scratch = nullptr;
+  const int rc = builtin_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  // Stage 1 rewrites every partial that stage 2 reads, so nothing in the shared array has to be
+  // cleared between calls; whatever the previous call left there is simply overwritten.
+  return layernorm_bwd_launch(dy, dy_dtype, x, w, mean, rstd, dres_in, dx, dx_lowp, dw, db, accumulate,
+                              scratch, sizeof(float) * kNoAllocMaxParts * 2 * kNoAllocMaxC, M, C, cs(stream));
+}
