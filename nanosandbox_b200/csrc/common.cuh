@@ -70,6 +70,30 @@ __device__ __forceinline__ float gelu_exact_grad(float x) {
   return cdf + x * pdf;
 }
 
+// Fast variants for bf16 outputs (rounded to 8 mantissa bits afterwards): erf by Abramowitz-Stegun
+// 7.1.26 (|error| < 1.5e-7) sharing one exp with the Gaussian density.
+__device__ __forceinline__ float gelu_fast_parts(float x, float& pdf_unscaled) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  const float e = __expf(-z * z);  // = exp(-x^2 / 2)
+  float p = fmaf(t, 1.061405429f, -1.453152027f);
+  p = fmaf(t, p, 1.421413741f);
+  p = fmaf(t, p, -0.284496736f);
+  p = fmaf(t, p, 0.254829592f);
+  const float erf_abs = 1.0f - p * t * e;
+  pdf_unscaled = e;
+  return 0.5f * (1.0f + copysignf(erf_abs, x));  // Phi(x)
+}
+__device__ __forceinline__ float gelu_fast(float x) {
+  float e;
+  return x * gelu_fast_parts(x, e);
+}
+__device__ __forceinline__ float gelu_fast_grad(float x) {
+  float e;
+  const float cdf = gelu_fast_parts(x, e);
+  return fmaf(x * 0.39894228040143267794f, e, cdf);
+}
+
 // 128-bit streaming loads/stores (read-once data: keep it out of L1)
 __device__ __forceinline__ uint4 ld_stream(const void* p) {
   uint4 r;

@@ -7,10 +7,13 @@
 //   * K-major or MN-major operands (weight-gradient GEMMs read dY and X "transposed" in place
 //     through MN-major descriptors, no transpose pass),
 //   * split-K for the short-and-wide weight-gradient shapes (fp32 red.global.add epilogue),
-//   * fused epilogues (bias, exact GELU forward/backward, residual add, fp32 accumulate).
+//   * fused epilogues (bias, exact GELU forward/backward, residual add, fp32 accumulate); the
+//     output tile leaves through swizzled shared-memory staging buffers and TMA stores (TMA
+//     reduce-add for accumulation / split-K), residual and pre-activation tiles arrive by TMA,
+//     prefetched several chunks ahead, so every global access of the epilogue is a full line.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
-// warps 2..5 = epilogue (TMEM -> registers -> global), one TMEM lane quarter each.
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..5 (and 6..9 for the ALU-heavy GELU epilogues) = epilogue, one TMEM lane quarter each.
 #include <mutex>
 #include <unordered_map>
 
@@ -22,10 +25,14 @@ namespace nsb {
 namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kThreads = 192;
-__host__ __device__ constexpr int stages_for(int bn) { return bn == 256 ? 4 : 6; }
-constexpr size_t smem_bytes_for(int bn) {
-  return static_cast<size_t>(stages_for(bn)) * (BM * BK * 2 + bn * BK * 2) + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kThreads = 320;  // TMA warp, MMA warp, 2 x 4 epilogue warps
+constexpr int kMaxStages = 8;
+constexpr int kMaxBuf = 8;
+constexpr int STG_BYTES = 128 * 128;  // one epilogue staging buffer: 128 rows x 128 B (swizzled)
+constexpr size_t kSmemLimit = 232448;  // 227 KB opt-in maximum per CTA
+inline size_t smem_bytes_for(int bn, int stages, int nbuf) {
+  return static_cast<size_t>(stages) * (BM * BK * 2 + bn * BK * 2) + static_cast<size_t>(nbuf) * STG_BYTES +
+         1024 /*align*/ + 256 /*barriers*/;
 }
 }  // namespace
 
@@ -164,11 +171,25 @@ __device__ __forceinline__ void epilogue_row32(const EpiParams& p, int m, int n,
 }
 
 // ---- the kernel -------------------------------------------------------------------------------
+struct TileCoord { int m_blk, n_blk, split; };
+__device__ __forceinline__ TileCoord tile_of(int w, int num_m, int num_n) {
+  TileCoord t;
+  t.m_blk = w % num_m;
+  const int rest = w / num_m;
+  t.n_blk = rest % num_n;
+  t.split = rest / num_n;
+  return t;
+}
+__device__ __forceinline__ uint32_t stg_off(int row, int q) {  // 16-byte chunk q of a 128-byte row
+  return static_cast<uint32_t>(row * 128 + ((q ^ (row & 7)) << 4));
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                   int K, int num_m, int num_n, int splits, int kb_per_split, EpiParams ep) {
-  constexpr int STAGES = stages_for(BN);
+                   const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
+                   const __grid_constant__ CUtensorMap tma_aux, int K, int num_m, int num_n, int splits,
+                   int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, EpiParams ep) {
   constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN;
   constexpr uint32_t IDESC = ptx::umma_idesc_bf16(BM, BN, A_MN, B_MN);
@@ -176,13 +197,15 @@ __global__ void __launch_bounds__(kThreads, 1)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + STAGES * A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES));
+  uint8_t* smem_b = smem_a + stages * A_BYTES;
+  uint8_t* smem_stg = smem_b + stages * B_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stg + ngroups * nbuf * STG_BYTES);
   uint64_t* full = bars;
-  uint64_t* empty = bars + STAGES;
-  uint64_t* tfull = bars + 2 * STAGES;
-  uint64_t* tempty = bars + 2 * STAGES + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* empty = bars + kMaxStages;
+  uint64_t* tfull = bars + 2 * kMaxStages;
+  uint64_t* tempty = tfull + 2;
+  uint64_t* auxfull = tempty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(auxfull + kMaxBuf);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_kb = (K + BK - 1) / BK;
@@ -191,14 +214,20 @@ __global__ void __launch_bounds__(kThreads, 1)
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tma_a);
     ptx::prefetch_tmap(&tma_b);
-    for (int s = 0; s < STAGES; ++s) {
+    if (tma_epi) {
+      ptx::prefetch_tmap(&tma_c);
+      if (ep.kind == NSB_EPI_GELU) ptx::prefetch_tmap(&tma_c2);
+      if (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU) ptx::prefetch_tmap(&tma_aux);
+    }
+    for (int s = 0; s < stages; ++s) {
       ptx::mbar_init(&full[s], 1);
       ptx::mbar_init(&empty[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 4);
+      ptx::mbar_init(&tempty[s], 4 * ngroups);
     }
+    for (int s = 0; s < kMaxBuf; ++s) ptx::mbar_init(&auxfull[s], 1);
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
@@ -213,9 +242,8 @@ __global__ void __launch_bounds__(kThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-        const int m_blk = w % num_m, rest = w / num_m;
-        const int n_blk = rest % num_n, split = rest / num_n;
-        const int kb0 = split * kb_per_split;
+        const TileCoord t = tile_of(w, num_m, num_n);
+        const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&empty[stage], phase ^ 1);
@@ -225,18 +253,18 @@ __global__ void __launch_bounds__(kThreads, 1)
           if (A_MN) {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              ptx::tma_load_2d(a_dst + j * (64 * BK * 2), &tma_a, &full[stage], m_blk * BM + j * 64, kb * BK);
+              ptx::tma_load_2d(a_dst + j * (64 * BK * 2), &tma_a, &full[stage], t.m_blk * BM + j * 64, kb * BK);
           } else {
-            ptx::tma_load_2d(a_dst, &tma_a, &full[stage], kb * BK, m_blk * BM);
+            ptx::tma_load_2d(a_dst, &tma_a, &full[stage], kb * BK, t.m_blk * BM);
           }
           if (B_MN) {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
-              ptx::tma_load_2d(b_dst + j * (64 * BK * 2), &tma_b, &full[stage], n_blk * BN + j * 64, kb * BK);
+              ptx::tma_load_2d(b_dst + j * (64 * BK * 2), &tma_b, &full[stage], t.n_blk * BN + j * 64, kb * BK);
           } else {
-            ptx::tma_load_2d(b_dst, &tma_b, &full[stage], kb * BK, n_blk * BN);
+            ptx::tma_load_2d(b_dst, &tma_b, &full[stage], kb * BK, t.n_blk * BN);
           }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == stages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -248,8 +276,8 @@ __global__ void __launch_bounds__(kThreads, 1)
       int as = 0;
       uint32_t aphase = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-        const int split = (w / num_m) / num_n;
-        const int kb0 = split * kb_per_split;
+        const TileCoord t = tile_of(w, num_m, num_n);
+        const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         ptx::mbar_wait(&tempty[as], aphase ^ 1);
         ptx::tc_fence_after();
@@ -272,7 +300,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             ptx::umma_bf16(d_tmem, a_k, b_k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           ptx::umma_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == stages) { stage = 0; phase ^= 1; }
         }
         ptx::umma_commit(&tfull[as]);       // accumulator complete -> epilogue
         if (++as == 2) { as = 0; aphase ^= 1; }
@@ -280,26 +308,197 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
   } else {
     // ================================ epilogue ==============================================
-    const int q = warp & 3;  // TMEM lane quarter this warp may touch
+    // One or two groups of four warps; a group covers all 128 TMEM lanes (one lane quarter per
+    // warp) and takes every ngroups-th column chunk of a tile.
+    const int grp = (warp - 2) >> 2;
+    const int q = warp & 3;                 // TMEM lane quarter this warp may touch
+    const int row = q * 32 + lane;          // row of the tile owned by this thread
+    const int et = (threadIdx.x - 64) & 127;  // 0..127 within the group
     const float alpha = ep.alpha ? *ep.alpha : 1.f;
-    const bool use_atomics = (ep.kind == NSB_EPI_ACCUM) && splits > 1;
     int as = 0;
     uint32_t aphase = 0;
-    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-      const int m_blk = w % num_m, n_blk = (w / num_m) % num_n;
-      ptx::mbar_wait(&tfull[as], aphase);
-      ptx::tc_fence_after();
-      const int m = m_blk * BM + q * 32 + lane;
+    if (grp >= ngroups) {
+      // idle warps of the second group
+    } else if (!tma_epi) {
+      // ---- direct-store fallback (outputs whose row stride is not a multiple of 16 bytes) ----
+      const bool use_atomics = (ep.kind == NSB_EPI_ACCUM) && splits > 1;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const TileCoord t = tile_of(w, num_m, num_n);
+        ptx::mbar_wait(&tfull[as], aphase);
+        ptx::tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        float v[32];
-        ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN + c * 32), v);
-        epilogue_row32(ep, m, n_blk * BN + c * 32, v, alpha, use_atomics);
+        for (int c = grp; c < BN / 32; c += ngroups) {
+          float v[32];
+          ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN + c * 32), v);
+          epilogue_row32(ep, t.m_blk * BM + row, t.n_blk * BN + c * 32, v, alpha, use_atomics);
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&tempty[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tempty[as]);
-      if (++as == 2) { as = 0; aphase ^= 1; }
+    } else {
+      // ---- staged epilogue: TMEM -> registers -> swizzled smem -> TMA store / reduce-add ----
+      const bool c32 = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_ACCUM || !ep.c_bf16);
+      const int CW = c32 ? 32 : 64;         // columns per 128-byte staging row
+      const int CH = BN / CW;               // chunks per tile
+      const int CHG = CH / ngroups;         // chunks per tile handled by this group
+      const bool aux_tma = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU) && !aux_direct;
+      const bool reduce = (ep.kind == NSB_EPI_ACCUM) && (ep.accumulate || splits > 1);
+      const bool has_bias = ep.bias != nullptr && ep.kind != NSB_EPI_ACCUM && ep.kind != NSB_EPI_DGELU;
+      const int my_tiles = (total_work - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+      const int total_chunks = my_tiles * CHG;
+      uint8_t* pool = smem_stg + grp * nbuf * STG_BYTES;
+      uint64_t* auxbar = auxfull + grp * nbuf;
+      const int bar_id = 1 + grp;
+      int emit = 0;                         // staging-buffer uses so far (buffer = emit % nbuf)
+      int next_aux = 0;                     // next (group-local) chunk whose aux tile was not requested yet
+      auto prefetch_aux = [&](int upto) {   // elected thread only
+        while (next_aux <= upto && next_aux < total_chunks) {
+          const int j = next_aux++;
+          const TileCoord t = tile_of(static_cast<int>(blockIdx.x) + (j / CHG) * static_cast<int>(gridDim.x), num_m, num_n);
+          const int b = j % nbuf;
+          ptx::mbar_expect_tx(&auxbar[b], STG_BYTES);
+          ptx::tma_load_2d(pool + b * STG_BYTES, &tma_aux, &auxbar[b],
+                           t.n_blk * BN + ((j % CHG) * ngroups + grp) * CW, t.m_blk * BM);
+        }
+      };
+      // make the staged data visible to the async proxy, wait until the buffer about to be
+      // reused is drained, then one thread issues the store
+      auto emit_store = [&](const CUtensorMap* map, int col, int rowg, bool red) {
+        ptx::fence_proxy_async();
+        if (et == 0) ptx::bulk_wait_read<0>();
+        ptx::named_bar_sync(bar_id, 128);
+        if (et == 0) {
+          const uint8_t* src = pool + (emit % nbuf) * STG_BYTES;
+          if (red) ptx::tma_reduce_add_2d(map, src, col, rowg);
+          else ptx::tma_store_2d(map, src, col, rowg);
+          ptx::bulk_commit();
+        }
+        ++emit;
+      };
+      if (aux_tma && et == 0) prefetch_aux(nbuf - 1);
+      int g = 0;                            // group-local chunk counter (aux kinds: emit == g)
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const TileCoord t = tile_of(w, num_m, num_n);
+        ptx::mbar_wait(&tfull[as], aphase);
+        ptx::tc_fence_after();
+        const int m0 = t.m_blk * BM;
+#pragma unroll 1
+        for (int c = grp; c < CH; c += ngroups, ++g) {
+          const int n0 = t.n_blk * BN + c * CW;
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN + c * CW);
+          uint8_t* buf = pool + (emit % nbuf) * STG_BYTES;
+          if (c32) {
+            float v[32];
+            ptx::tmem_ld_32x32(taddr, v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= alpha;
+            if (has_bias) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] += (n0 + j < ep.N) ? __ldg(ep.bias + n0 + j) : 0.f;
+            }
+            if (ep.kind == NSB_EPI_RESIDUAL) {
+              ptx::mbar_wait(&auxbar[g % nbuf], (g / nbuf) & 1);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 a = *reinterpret_cast<const float4*>(buf + stg_off(row, j));
+                if (ep.c_bf16) {
+                  v[4 * j] = a.x + round_bf16(v[4 * j]); v[4 * j + 1] = a.y + round_bf16(v[4 * j + 1]);
+                  v[4 * j + 2] = a.z + round_bf16(v[4 * j + 2]); v[4 * j + 3] = a.w + round_bf16(v[4 * j + 3]);
+                } else {
+                  v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
+                }
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *reinterpret_cast<float4*>(buf + stg_off(row, j)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            emit_store(&tma_c, n0, m0, reduce);
+            if (ep.kind == NSB_EPI_GELU) {  // fp32 C2 (not used by the bf16 model path, kept complete)
+              buf = pool + (emit % nbuf) * STG_BYTES;
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(buf + stg_off(row, j)) =
+                    make_float4(gelu_exact(v[4 * j]), gelu_exact(v[4 * j + 1]), gelu_exact(v[4 * j + 2]), gelu_exact(v[4 * j + 3]));
+              emit_store(&tma_c2, n0, m0, false);
+            }
+          } else {
+            // bf16 output: 64 columns per staging row, processed as two 32-column halves.
+            // GELU: a second pass re-reads the accumulators from TMEM for the activated output.
+            const int npass = (ep.kind == NSB_EPI_GELU) ? 2 : 1;
+            for (int pass = 0; pass < npass; ++pass) {
+              if (pass == 1) buf = pool + (emit % nbuf) * STG_BYTES;
+              if (ep.kind == NSB_EPI_DGELU && aux_tma) ptx::mbar_wait(&auxbar[g % nbuf], (g / nbuf) & 1);
+#pragma unroll 1
+              for (int half = 0; half < 2; ++half) {
+                const int nh = n0 + half * 32;
+                uint4 hraw[4];
+                if (ep.kind == NSB_EPI_DGELU) {
+                  if (aux_tma) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) hraw[j] = *reinterpret_cast<const uint4*>(buf + stg_off(row, half * 4 + j));
+                  } else {
+                    // pre-activation read straight from global: 64 contiguous bytes of this thread's row
+                    const bool ok = (m0 + row < ep.M) && (nh + 32 <= ep.N);
+                    const uint4* hp = reinterpret_cast<const uint4*>(
+                        static_cast<const __nv_bfloat16*>(ep.aux) + static_cast<size_t>(ok ? m0 + row : 0) * ep.ldc + (ok ? nh : 0));
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) hraw[j] = ok ? __ldg(hp + j) : make_uint4(0, 0, 0, 0);
+                    if (!ok && (m0 + row < ep.M)) {  // ragged right edge: element-wise
+                      __nv_bfloat16 tmp[32];
+                      for (int j = 0; j < 32; ++j)
+                        tmp[j] = (nh + j < ep.N) ? static_cast<const __nv_bfloat16*>(ep.aux)[static_cast<size_t>(m0 + row) * ep.ldc + nh + j]
+                                                 : __float2bfloat16_rn(0.f);
+#pragma unroll
+                      for (int j = 0; j < 4; ++j) hraw[j] = reinterpret_cast<const uint4*>(tmp)[j];
+                    }
+                  }
+                }
+                float v[32];
+                ptx::tmem_ld_32x32(taddr + half * 32, v);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] *= alpha;
+                if (has_bias) {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) v[j] += (nh + j < ep.N) ? __ldg(ep.bias + nh + j) : 0.f;
+                }
+                if (ep.kind == NSB_EPI_DGELU) {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    const float2 h0 = unpack_bf16x2(hraw[j].x), h1 = unpack_bf16x2(hraw[j].y),
+                                 h2 = unpack_bf16x2(hraw[j].z), h3 = unpack_bf16x2(hraw[j].w);
+                    v[8 * j] = round_bf16(v[8 * j]) * gelu_fast_grad(h0.x);
+                    v[8 * j + 1] = round_bf16(v[8 * j + 1]) * gelu_fast_grad(h0.y);
+                    v[8 * j + 2] = round_bf16(v[8 * j + 2]) * gelu_fast_grad(h1.x);
+                    v[8 * j + 3] = round_bf16(v[8 * j + 3]) * gelu_fast_grad(h1.y);
+                    v[8 * j + 4] = round_bf16(v[8 * j + 4]) * gelu_fast_grad(h2.x);
+                    v[8 * j + 5] = round_bf16(v[8 * j + 5]) * gelu_fast_grad(h2.y);
+                    v[8 * j + 6] = round_bf16(v[8 * j + 6]) * gelu_fast_grad(h3.x);
+                    v[8 * j + 7] = round_bf16(v[8 * j + 7]) * gelu_fast_grad(h3.y);
+                  }
+                } else if (pass == 1) {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) v[j] = gelu_fast(round_bf16(v[j]));
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  *reinterpret_cast<uint4*>(buf + stg_off(row, half * 4 + j)) =
+                      make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                 pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+              }
+              emit_store(pass == 0 ? &tma_c : &tma_c2, n0, m0, false);
+            }
+          }
+          // stores up to chunk g-1 have drained (emit_store waited): their buffers may be refilled
+          if (aux_tma && et == 0) prefetch_aux(g + nbuf - 1);
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&tempty[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+      if (et == 0) ptx::bulk_wait_all();
     }
   }
 
@@ -328,16 +527,16 @@ EncodeTiledFn get_encode_fn() {
 }
 
 struct MapKey {
-  const void* ptr; uint64_t d0, d1, stride; uint32_t b0, b1;
+  const void* ptr; uint64_t d0, d1, stride; uint32_t b0, b1, esize;
   bool operator==(const MapKey& o) const {
-    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && stride == o.stride && b0 == o.b0 && b1 == o.b1;
+    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && stride == o.stride && b0 == o.b0 && b1 == o.b1 && esize == o.esize;
   }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     size_t h = reinterpret_cast<size_t>(k.ptr);
     auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
-    mix(k.d0); mix(k.d1); mix(k.stride); mix(k.b0); mix(k.b1);
+    mix(k.d0); mix(k.d1); mix(k.stride); mix(k.b0); mix(k.b1); mix(k.esize);
     return h;
   }
 };
@@ -345,10 +544,11 @@ std::mutex g_map_mu;
 std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 }  // namespace
 
-// 2-D bf16 tensor [d1 rows][d0 contiguous], row stride in elements, box {b0, b1}, 128B swizzle
-int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t row_stride,
-                      uint32_t b0, uint32_t b1) {
-  MapKey key{ptr, d0, d1, row_stride, b0, b1};
+// 2-D tensor [d1 rows][d0 contiguous] of bf16 (esize 2) or fp32 (esize 4), row stride in elements,
+// box {b0, b1}, 128-byte swizzle (b0 * esize must be 128)
+int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint64_t d1, uint64_t row_stride,
+                 uint32_t b0, uint32_t b1) {
+  MapKey key{ptr, d0, d1, row_stride, b0, b1, static_cast<uint32_t>(esize)};
   {
     std::lock_guard<std::mutex> g(g_map_mu);
     auto it = g_maps.find(key);
@@ -356,16 +556,16 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d
   }
   EncodeTiledFn fn = get_encode_fn();
   NSB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
-  NSB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (row_stride * 2) % 16 == 0,
-              "gemm: bf16 operand must be 16-byte aligned with a row stride multiple of 8 elements (stride %llu)",
+  NSB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (row_stride * esize) % 16 == 0,
+              "gemm: operand must be 16-byte aligned with a row stride multiple of 16 bytes (stride %llu elements)",
               static_cast<unsigned long long>(row_stride));
   cuuint64_t gdim[2] = {d0, d1};
-  cuuint64_t gstr[1] = {row_stride * 2};
+  cuuint64_t gstr[1] = {row_stride * static_cast<uint64_t>(esize)};
   cuuint32_t box[2] = {b0, b1};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(out, esize == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  const_cast<void*>(ptr), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   NSB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (dims %llu x %llu, stride %llu)",
               static_cast<int>(r), static_cast<unsigned long long>(d0), static_cast<unsigned long long>(d1),
               static_cast<unsigned long long>(row_stride));
@@ -375,34 +575,43 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d
   return 0;
 }
 
+struct LaunchPlan {
+  CUtensorMap ta, tb, tc, tc2, taux;
+  int K, num_m, num_n, splits, kb_per_split, stages, nbuf, tma_epi, ngroups, aux_direct;
+};
+
 template <int BN, bool A_MN, bool B_MN>
-static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, int K, int num_m, int num_n, int splits,
-                          int kb_per_split, const EpiParams& ep, cudaStream_t stream) {
+static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_t stream) {
   auto kern = gemm_tc_kernel<BN, A_MN, B_MN>;
   static bool attr_done = false;
-  const size_t smem = smem_bytes_for(BN);
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemLimit));
     NSB_REQUIRE(e == cudaSuccess, "gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     attr_done = true;
   }
-  const int total = num_m * num_n * splits;
+  const size_t smem = smem_bytes_for(BN, lp.stages, lp.nbuf * lp.ngroups);
+  const int total = lp.num_m * lp.num_n * lp.splits;
   const int grid = total < sm_count() ? total : sm_count();
-  kern<<<grid, kThreads, smem, stream>>>(ta, tb, K, num_m, num_n, splits, kb_per_split, ep);
+  kern<<<grid, kThreads, smem, stream>>>(lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
+                                          lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, ep);
   count_launch();
   return check_launch("gemm_tc");
 }
 
-int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t stream, int force_bn, int force_splits) {
+int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t stream, int force_bn, int force_splits,
+                   int force_direct_epi, int force_groups) {
   const int M = a->M, N = a->N, K = a->K;
   int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
   if (force_bn == 128 || force_bn == 256) bn = force_bn;
-  const int num_m = (M + BM - 1) / BM, num_n = (N + bn - 1) / bn;
+  LaunchPlan lp;
+  lp.K = K;
+  lp.num_m = (M + BM - 1) / BM;
+  lp.num_n = (N + bn - 1) / bn;
   const int total_kb = (K + BK - 1) / BK;
-  // split-K only where the epilogue can accumulate atomically into a pre-existing fp32 C
+  // split-K only where the epilogue can accumulate into a pre-existing fp32 C
   int splits = 1;
   if (ep.kind == NSB_EPI_ACCUM && ep.accumulate) {
-    const int tiles = num_m * num_n, sms = sm_count();
+    const int tiles = lp.num_m * lp.num_n, sms = sm_count();
     if (tiles < sms) {
       splits = (2 * sms + tiles - 1) / tiles;
       const int max_splits = total_kb / 8 > 0 ? total_kb / 8 : 1;  // keep >= 8 k-blocks per split
@@ -414,18 +623,47 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   if (kb_per_split < 1) kb_per_split = 1;
   splits = (total_kb + kb_per_split - 1) / kb_per_split;
   if (splits < 1) splits = 1;
+  lp.splits = splits;
+  lp.kb_per_split = kb_per_split;
 
-  CUtensorMap ta, tb;
   int rc;
-  if (a->a_kmajor) rc = make_tmap_bf16_2d(&ta, a->A, K, M, a->lda, BK, BM);
-  else             rc = make_tmap_bf16_2d(&ta, a->A, M, K, a->lda, 64, BK);
+  if (a->a_kmajor) rc = make_tmap_2d(&lp.ta, a->A, 2, K, M, a->lda, BK, BM);
+  else             rc = make_tmap_2d(&lp.ta, a->A, 2, M, K, a->lda, 64, BK);
   if (rc) return rc;
-  if (a->b_kmajor) rc = make_tmap_bf16_2d(&tb, a->B, K, N, a->ldb, BK, bn);
-  else             rc = make_tmap_bf16_2d(&tb, a->B, N, K, a->ldb, 64, BK);
+  if (a->b_kmajor) rc = make_tmap_2d(&lp.tb, a->B, 2, K, N, a->ldb, BK, bn);
+  else             rc = make_tmap_2d(&lp.tb, a->B, 2, N, K, a->ldb, 64, BK);
   if (rc) return rc;
 
-#define NSB_GEMM_CASE(BNV, AMN, BMN) \
-  return launch_variant<BNV, AMN, BMN>(ta, tb, K, num_m, num_n, splits, kb_per_split, ep, stream)
+  // staged (TMA) epilogue whenever every output/aux row is 16-byte addressable
+  const bool c32 = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_ACCUM || !ep.c_bf16);
+  const int cesz = c32 ? 4 : 2;
+  const bool has_aux = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU);
+  auto tma_ok = [&](const void* p, int esz) {
+    return p != nullptr && (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (static_cast<size_t>(a->ldc) * esz) % 16 == 0;
+  };
+  bool tma_epi = !force_direct_epi && tma_ok(a->C, cesz);
+  if (ep.kind == NSB_EPI_GELU) tma_epi = tma_epi && tma_ok(a->C2, cesz);
+  if (has_aux) tma_epi = tma_epi && tma_ok(a->aux, ep.kind == NSB_EPI_RESIDUAL ? 4 : 2);
+  lp.tma_epi = tma_epi ? 1 : 0;
+  lp.tc = lp.ta; lp.tc2 = lp.ta; lp.taux = lp.ta;  // placeholders when unused
+  if (tma_epi) {
+    const uint32_t cw = c32 ? 32 : 64;
+    rc = make_tmap_2d(&lp.tc, a->C, cesz, N, M, a->ldc, cw, BM);
+    if (rc) return rc;
+    if (ep.kind == NSB_EPI_GELU) { rc = make_tmap_2d(&lp.tc2, a->C2, cesz, N, M, a->ldc, cw, BM); if (rc) return rc; }
+    if (has_aux) { rc = make_tmap_2d(&lp.taux, a->aux, ep.kind == NSB_EPI_RESIDUAL ? 4 : 2, N, M, a->ldc, cw, BM); if (rc) return rc; }
+  }
+  // ALU-heavy bf16 GELU epilogues get a second epilogue group; GELU backward then reads its
+  // pre-activation tile straight from global (no aux staging buffers)
+  const bool heavy = tma_epi && ep.c_bf16 && (ep.kind == NSB_EPI_GELU || ep.kind == NSB_EPI_DGELU);
+  lp.ngroups = (heavy && force_groups != 1) || (tma_epi && force_groups == 2 && ep.kind != NSB_EPI_RESIDUAL) ? 2 : 1;
+  lp.aux_direct = (ep.kind == NSB_EPI_DGELU && lp.ngroups == 2) ? 1 : 0;
+  lp.nbuf = tma_epi ? ((has_aux && !lp.aux_direct) ? 4 : 2) : 0;
+  int stages = kMaxStages;
+  while (stages > 2 && smem_bytes_for(bn, stages, lp.nbuf * lp.ngroups) > kSmemLimit) --stages;
+  lp.stages = stages;
+
+#define NSB_GEMM_CASE(BNV, AMN, BMN) return launch_variant<BNV, AMN, BMN>(lp, ep, stream)
   const bool amn = !a->a_kmajor, bmn = !a->b_kmajor;
   if (bn == 256) {
     if (!amn && !bmn) NSB_GEMM_CASE(256, false, false);
@@ -447,16 +685,19 @@ int gemm_simt_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t s
 
 using namespace nsb;
 
-static int g_force_bn = 0, g_force_splits = 0, g_force_simt = 0;
+static int g_force_bn = 0, g_force_splits = 0, g_force_simt = 0, g_force_direct_epi = 0, g_force_groups = 0;
 
 extern "C" {
 
 // test/tuning hooks (not part of the reference-facing surface): force the N tile, the split-K
-// factor, or route bf16 GEMMs through the SIMT kernel (debug cross-check).
+// factor, route bf16 GEMMs through the SIMT kernel (force_simt = 1), or force the direct-store
+// epilogue (force_simt = 2) for cross-checks.
 void nsb_gemm_debug_config(int force_bn, int force_splits, int force_simt) {
   g_force_bn = force_bn;
   g_force_splits = force_splits;
-  g_force_simt = force_simt;
+  g_force_simt = force_simt == 1;
+  g_force_direct_epi = force_simt == 2;
+  g_force_groups = force_simt == 3 ? 1 : (force_simt == 4 ? 2 : 0);  // 3: one epilogue group, 4: two
 }
 
 int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
@@ -473,7 +714,7 @@ int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
   ep.bias = a->bias; ep.alpha = a->alpha; ep.ldc = a->ldc; ep.c_bf16 = (a->c_dtype == NSB_BF16) ? 1 : 0;
   ep.accumulate = a->accumulate;
   if (a->in_dtype == NSB_F32 || g_force_simt) return gemm_simt_launch(a, ep, cs(stream));
-  return gemm_tc_launch(a, ep, cs(stream), g_force_bn, g_force_splits);
+  return gemm_tc_launch(a, ep, cs(stream), g_force_bn, g_force_splits, g_force_direct_epi, g_force_groups);
 }
 
 }  // extern "C"

@@ -142,10 +142,13 @@ class _FusedStep(torch.autograd.Function):
         logits, loss = model._engine_forward(idx, targets)
         ctx.model = model
         ctx.mark_non_differentiable(logits)
+        ctx.set_materialize_grads(False)  # no [B,T,V] zeros tensor for the unused logits gradient
         return logits, loss
 
     @staticmethod
     def backward(ctx, _glogits, gloss):
+        if gloss is None:
+            return None, None, None, None
         ctx.model._engine_backward(gloss)
         return None, None, None, None
 

@@ -249,6 +249,41 @@ def test_gemm_epilogues(dt, epi, bias):
     _gemm_case(dt, 640, 768, 256, True, True, epi, bias=bias and epi != _lib.EPI_DGELU, alpha=0.5 if epi == _lib.EPI_DGELU else None)
 
 
+@pytest.mark.parametrize("epi", [_lib.EPI_STORE, _lib.EPI_GELU, _lib.EPI_RESIDUAL, _lib.EPI_DGELU, _lib.EPI_ACCUM])
+@pytest.mark.parametrize("M,N,K", [(8192, 1024, 128), (4000, 1160, 192), (2048, 2304, 64)])
+def test_gemm_tc_epilogues_many_tiles_per_cta(epi, M, N, K):
+    """> 148 tiles: every CTA walks several tiles (TMEM double buffering, staging-buffer reuse and
+    the aux prefetch running ahead across tile boundaries)."""
+    _gemm_case(torch.bfloat16, M, N, K, True, True, epi, bias=epi in (_lib.EPI_STORE, _lib.EPI_GELU, _lib.EPI_RESIDUAL),
+               accumulate=True, alpha=0.75)
+
+
+@pytest.mark.parametrize("groups", [3, 4])
+@pytest.mark.parametrize("epi", [_lib.EPI_STORE, _lib.EPI_GELU, _lib.EPI_RESIDUAL, _lib.EPI_DGELU, _lib.EPI_ACCUM])
+def test_gemm_tc_epilogue_group_count(epi, groups):
+    """One (3) and two (4) epilogue warp groups produce the same results, ragged edges included."""
+    lib = _lib.load()
+    lib.nsb_gemm_debug_config(0, 0, groups)
+    try:
+        _gemm_case(torch.bfloat16, 3000, 1000, 192, True, True, epi, bias=epi in (_lib.EPI_STORE, _lib.EPI_GELU),
+                   accumulate=True, alpha=0.5)
+        _gemm_case(torch.bfloat16, 8192, 1024, 128, True, False, epi, accumulate=True)
+    finally:
+        lib.nsb_gemm_debug_config(0, 0, 0)
+
+
+@pytest.mark.parametrize("epi", [_lib.EPI_STORE, _lib.EPI_GELU, _lib.EPI_RESIDUAL, _lib.EPI_DGELU, _lib.EPI_ACCUM])
+def test_gemm_tc_direct_epilogue_fallback(epi):
+    """The direct-store epilogue (used when an output row stride is not 16-byte addressable)."""
+    lib = _lib.load()
+    lib.nsb_gemm_debug_config(0, 0, 2)
+    try:
+        _gemm_case(torch.bfloat16, 1000, 520, 192, True, True, epi, bias=epi != _lib.EPI_DGELU and epi != _lib.EPI_ACCUM,
+                   accumulate=True)
+    finally:
+        lib.nsb_gemm_debug_config(0, 0, 0)
+
+
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("accumulate", [False, True])
 @pytest.mark.parametrize("M,N,K", [(768, 768, 4096), (2304, 768, 2048), (65, 384, 1024), (200, 120, 520)])
