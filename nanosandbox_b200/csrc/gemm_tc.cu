@@ -238,31 +238,32 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   if (warp == 0) {
     // ================================ TMA producer ==========================================
-    if (lane == 0) {
+    // lane 0 owns the barrier protocol; the boxes of a stage (up to 6 for MN-major operands) are
+    // issued by different lanes so that their descriptor/issue latencies overlap
+    {
       int stage = 0;
       uint32_t phase = 0;
+      constexpr int A_BOXES = A_MN ? BM / 64 : 1;
+      constexpr int B_BOXES = B_MN ? BN / 64 : 1;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const TileCoord t = tile_of(w, num_m, num_n);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait(&empty[stage], phase ^ 1);
-          ptx::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+          if (lane == 0) {
+            ptx::mbar_wait(&empty[stage], phase ^ 1);
+            ptx::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+          }
+          __syncwarp();
           uint8_t* a_dst = smem_a + stage * A_BYTES;
           uint8_t* b_dst = smem_b + stage * B_BYTES;
-          if (A_MN) {
-#pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              ptx::tma_load_2d(a_dst + j * (64 * BK * 2), &tma_a, &full[stage], t.m_blk * BM + j * 64, kb * BK);
-          } else {
-            ptx::tma_load_2d(a_dst, &tma_a, &full[stage], kb * BK, t.m_blk * BM);
-          }
-          if (B_MN) {
-#pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              ptx::tma_load_2d(b_dst + j * (64 * BK * 2), &tma_b, &full[stage], t.n_blk * BN + j * 64, kb * BK);
-          } else {
-            ptx::tma_load_2d(b_dst, &tma_b, &full[stage], kb * BK, t.n_blk * BN);
+          if (lane < A_BOXES) {
+            if (A_MN) ptx::tma_load_2d(a_dst + lane * (64 * BK * 2), &tma_a, &full[stage], t.m_blk * BM + lane * 64, kb * BK);
+            else ptx::tma_load_2d(a_dst, &tma_a, &full[stage], kb * BK, t.m_blk * BM);
+          } else if (lane < A_BOXES + B_BOXES) {
+            const int j = lane - A_BOXES;
+            if (B_MN) ptx::tma_load_2d(b_dst + j * (64 * BK * 2), &tma_b, &full[stage], t.n_blk * BN + j * 64, kb * BK);
+            else ptx::tma_load_2d(b_dst, &tma_b, &full[stage], kb * BK, t.n_blk * BN);
           }
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
@@ -608,14 +609,22 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   lp.num_m = (M + BM - 1) / BM;
   lp.num_n = (N + bn - 1) / bn;
   const int total_kb = (K + BK - 1) / BK;
-  // split-K only where the epilogue can accumulate into a pre-existing fp32 C
+  // split-K only where the epilogue can accumulate into a pre-existing fp32 C.  Pick the split that
+  // minimises waves x (k-blocks per split + fixed per-tile cost): wave quantisation matters more
+  // than the number of splits for the short-and-wide weight-gradient shapes.
   int splits = 1;
   if (ep.kind == NSB_EPI_ACCUM && ep.accumulate) {
     const int tiles = lp.num_m * lp.num_n, sms = sm_count();
-    if (tiles < sms) {
-      splits = (2 * sms + tiles - 1) / tiles;
-      const int max_splits = total_kb / 8 > 0 ? total_kb / 8 : 1;  // keep >= 8 k-blocks per split
-      if (splits > max_splits) splits = max_splits;
+    if (tiles < 2 * sms) {
+      double best = 1e30;
+      const int max_splits = total_kb / 4 > 0 ? (total_kb / 4 < 32 ? total_kb / 4 : 32) : 1;
+      for (int sp = 1; sp <= max_splits; ++sp) {
+        const int kbs = (total_kb + sp - 1) / sp;
+        const int real = (total_kb + kbs - 1) / kbs;
+        const int waves = (tiles * real + sms - 1) / sms;
+        const double cost = waves * (kbs + 14.0);  // ~14 k-block times of prologue/epilogue per tile
+        if (cost < best - 1e-9) { best = cost; splits = real; }
+      }
     }
     if (force_splits > 0) splits = force_splits;
   }
