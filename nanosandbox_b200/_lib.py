@@ -61,6 +61,7 @@ SIGNATURES = {
 DEBUG_SIGNATURES = {
     "nsb_gemm_debug_config": (None, [_I, _I, _I]),
     "nsb_attention_debug_config": (None, [_I]),
+    "nsb_attention_debug_timing": (None, [_P]),
 }
 
 _lib = None

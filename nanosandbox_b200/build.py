@@ -14,10 +14,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libnanosandbox_b200.so")
-SOURCES = ["elementwise.cu", "gemm_simt.cu", "gemm_tc.cu", "attention.cu"]
+SOURCES = ["elementwise.cu", "gemm_simt.cu", "gemm_tc.cu", "attention.cu", "attention_tc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC", "--use_fast_math=false"]
-NVCC_FLAGS = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+              "-Xcompiler", "-fPIC"]
 
 
 def _nvcc() -> str:
@@ -52,7 +51,7 @@ def build(force: bool = False, verbose: bool = True) -> str:
         subprocess.run(cmd, check=True)
         return obj
 
-    with ThreadPoolExecutor(max_workers=4) as ex:
+    with ThreadPoolExecutor(max_workers=5) as ex:
         objs = list(ex.map(compile_one, SOURCES))
     cmd = [nvcc, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     if verbose:

@@ -545,13 +545,19 @@ __global__ void __launch_bounds__(128)
 
 }  // namespace nsb
 
+namespace nsb {
+int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, int H, cudaStream_t stream);
+void attention_tc_set_debug_buffer(long long* p);
+}
 using namespace nsb;
 
-static int g_attn_force_simt = 0;
+static int g_attn_force_simt = 0;   // 1: exact SIMT kernels, 2: mma.sync flash kernels (cross-checks)
 
 extern "C" {
 
 void nsb_attention_debug_config(int force_simt) { g_attn_force_simt = force_simt; }
+// device buffer (>= 1024 int64) receiving phase timestamps of one CTA of the tcgen05 kernels; NULL = off
+void nsb_attention_debug_timing(void* device_buffer) { attention_tc_set_debug_buffer(static_cast<long long*>(device_buffer)); }
 
 int nsb_attention_fwd(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H, int D,
                       nsb_stream_t stream) {
@@ -559,7 +565,11 @@ int nsb_attention_fwd(const void* qkv, void* y, float* lse, int dtype, int B, in
   NSB_REQUIRE(D % 32 == 0 && D >= 32 && D <= 128, "attention_fwd: head dim %d unsupported (32/64/96/128)", D);
   if (B == 0 || T == 0) return 0;
   const float scale = 1.0f / sqrtf(static_cast<float>(D));
-  if (dtype == NSB_BF16 && D == 64 && !g_attn_force_simt) {
+  if (dtype == NSB_BF16 && D == 64 && g_attn_force_simt == 0) {
+    NSB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0, "attention_fwd: qkv must be 16-byte aligned");
+    return attention_fwd_tc_launch(qkv, y, lse, B, T, H, cs(stream));
+  }
+  if (dtype == NSB_BF16 && D == 64 && g_attn_force_simt == 2) {
     NSB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0, "attention_fwd: qkv must be 16-byte aligned");
     dim3 grid((T + 63) / 64, B * H);
     attn_fwd_mma<<<grid, 128, 0, cs(stream)>>>(static_cast<const __nv_bfloat16*>(qkv), static_cast<__nv_bfloat16*>(y),
@@ -590,7 +600,7 @@ int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const floa
   else
     attn_delta_kernel<__nv_bfloat16><<<rgrid, 256, 0, cs(stream)>>>(static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H, D);
   count_launch();
-  if (dtype == NSB_BF16 && D == 64 && !g_attn_force_simt) {
+  if (dtype == NSB_BF16 && D == 64 && g_attn_force_simt != 1) {
     NSB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(dy) & 15) == 0,
                 "attention_bwd: qkv/dy must be 16-byte aligned");
     const int smem_dkv = 6 * fa::TILE_BYTES + 2 * 128 * 4, smem_dq = 6 * fa::TILE_BYTES;

@@ -1,0 +1,331 @@
+// Causal flash attention on the 5th-gen tensor cores (bf16, head dim 64), forward pass.
+//
+// One CTA = 128 queries of one (batch, head); keys/values stream through in blocks of 128.
+//   S  = Q K^T     tcgen05.mma 128x128x16 x4, operands by TMA (K-major, 128B swizzle), S in TMEM
+//   P  = softmax   one thread per query row: tcgen05.ld of its S row, running max / sum in
+//                  registers (no shuffles), exp2, P written as bf16 into a swizzled smem tile
+//   O += P V       tcgen05.mma 128x64x16 x8, A = P (smem), B = V read MN-major in place; O stays
+//                  in TMEM for the whole key loop.  The running max used in the exponent is only
+//                  raised when the true max has grown by more than 2^8 (exact: softmax is shift
+//                  invariant), so the O accumulator is rescaled (tcgen05.ld/st by the row's own
+//                  thread) in the first block(s) only and the softmax warps never wait for P V.
+// Warp roles: warp 0 TMA producer (Q once, K/V double-buffered), warp 1 MMA issuer + TMEM owner,
+// warps 2..5 softmax / correction / output (one TMEM lane quarter each).  192 TMEM columns and
+// 112 KB of smem per CTA let two CTAs share an SM: one's softmax overlaps the other's MMAs.
+// q/k/v are read straight out of c_attn's [B, T, 3, H, 64] output through one tensor map.
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace nsb {
+
+int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint64_t d1, uint64_t row_stride,
+                 uint32_t b0, uint32_t b1);
+
+namespace fatc {
+constexpr int BQ = 128, BKV = 128, HD = 64;
+constexpr int TILE = BQ * HD * 2;          // 16 KB: 128 rows x 128 B
+constexpr int P_BYTES = BQ * BKV * 2;      // 32 KB: two 64-column swizzle atoms
+constexpr int KV_STAGES = 2;
+constexpr int SMEM_BYTES = TILE + KV_STAGES * 2 * TILE + P_BYTES + 256;
+constexpr uint32_t TMEM_COLS = 256;        // S: 128 columns, O block: 64 columns
+constexpr uint32_t S_COL = 0, O_COL = 128;
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t sw128(int row, int q16) {
+  return static_cast<uint32_t>(row * 128 + ((q16 ^ (row & 7)) << 4));
+}
+}  // namespace fatc
+
+// One pass over a 128-key block of one query row: P = exp2(S*scale - m) -> bf16 -> swizzled smem,
+// returning the row sum of P and (through mx) the raw row maximum.  `lim` (diagonal block only) is
+// the last key column this row may attend to.  TMEM loads are software-pipelined: the next
+// 32-column chunk is in flight while the current one is processed.
+template <bool DIAG>
+__device__ __forceinline__ float softmax_pass(uint32_t s_addr, uint8_t* sP, int row, int lim, float scale_log2,
+                                              float m, float& mx, uint64_t* pv_bar, uint32_t pv_parity) {
+  using namespace fatc;
+  float va[32], vb[32];
+  float s0 = 0.f, s1 = 0.f;
+  mx = -INFINITY;
+  ptx::tmem_ld_32x32_async(s_addr, va);
+  ptx::tmem_wait_ld32(va);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    float* cur = (c & 1) ? vb : va;
+    float* nxt = (c & 1) ? va : vb;
+    if (c < 3) ptx::tmem_ld_32x32_async(s_addr + (c + 1) * 32, nxt);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      if (DIAG) { if (c * 32 + i <= lim) mx = fmaxf(mx, cur[i]); }
+      else mx = fmaxf(mx, cur[i]);
+      float p = ex2(fmaf(cur[i], scale_log2, -m));
+      if (DIAG) { if (c * 32 + i > lim) p = 0.f; }
+      cur[i] = p;
+      if (i & 1) s1 += p; else s0 += p;
+    }
+    uint8_t* atom = sP + (c >> 1) * TILE;
+    // the previous block's P V may still be reading this tile: wait right before the first store
+    if (c == 0 && pv_bar != nullptr) ptx::mbar_wait(pv_bar, pv_parity);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      *reinterpret_cast<uint4*>(atom + sw128(row, (c & 1) * 4 + i)) =
+          make_uint4(pack_bf16x2(cur[8 * i], cur[8 * i + 1]), pack_bf16x2(cur[8 * i + 2], cur[8 * i + 3]),
+                     pack_bf16x2(cur[8 * i + 4], cur[8 * i + 5]), pack_bf16x2(cur[8 * i + 6], cur[8 * i + 7]));
+    if (c < 3) ptx::tmem_wait_ld32(nxt);
+  }
+  return s0 + s1;
+}
+
+// Running-softmax update for one block.  The exponent reference m is "lazy": the common case is a
+// single pass with the current m; only when some row's maximum outgrew it by more than 2^8 (always
+// in the first block) is m raised, the pass repeated and the O accumulator rescaled.  Exact, since
+// softmax is shift invariant; P stays below 2^8.  Returns the O rescale factor (1 = none).
+template <bool DIAG>
+__device__ __forceinline__ float softmax_block(uint32_t s_addr, uint8_t* sP, int row, int lim, float scale_log2,
+                                               float& m, float& l, bool first, uint64_t* pv_bar, uint32_t pv_parity) {
+  float mx;
+  float sum = 0.f;
+  if (!first) sum = softmax_pass<DIAG>(s_addr, sP, row, lim, scale_log2, m, mx, pv_bar, pv_parity);
+  else {
+    // first block: only the maximum is needed (m = -inf would make every P infinite)
+    float va[32];
+    mx = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      ptx::tmem_ld_32x32(s_addr + c * 32, va);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        if (DIAG) { if (c * 32 + i <= lim) mx = fmaxf(mx, va[i]); }
+        else mx = fmaxf(mx, va[i]);
+      }
+    }
+  }
+  float corr = 1.f;
+  const float m_true = mx * scale_log2;
+  const bool grow = m_true > m + 8.f;
+  if (__any_sync(0xffffffffu, grow)) {               // warp-uniform (TMEM loads are warp-collective)
+    if (grow) {
+      corr = fatc::ex2(m - m_true);                  // first block: exp2(-inf) = 0
+      l *= corr;
+      m = m_true;
+    }
+    float dummy;
+    // (a repeated pass finds the previous P V retired already: the first pass waited for it)
+    sum = softmax_pass<DIAG>(s_addr, sP, row, lim, scale_log2, m, dummy, nullptr, 0);
+  }
+  l += sum;
+  return corr;
+}
+
+// Optional phase timestamps (clock64) of CTA (0,0): softmax warp 2 lane 0 writes 4 stamps per key
+// block at dbg[0..], the MMA thread 4 stamps per block at dbg[512..].  NULL in production.
+__global__ void __launch_bounds__(192, 2)
+    attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ y,
+                       float* __restrict__ lse, int Tn, int H, float scale_log2, long long* dbg) {
+  using namespace fatc;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sQ = smem;
+  uint8_t* sKV = smem + TILE;                       // stage s: K at s*2*TILE, V at s*2*TILE + TILE
+  uint8_t* sP = sKV + KV_STAGES * 2 * TILE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + P_BYTES);
+  uint64_t* q_full = bars;
+  uint64_t* kv_full = bars + 1;                     // [2]
+  uint64_t* kv_empty = bars + 3;                    // [2]
+  uint64_t* s_full = bars + 5;
+  uint64_t* p_full = bars + 6;
+  uint64_t* o_full = bars + 7;
+  uint64_t* pv_done = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int C = H * HD;
+  const int qb = gridDim.y - 1 - blockIdx.y;        // longest query blocks of ALL heads are scheduled first
+  const int bh = blockIdx.x, b = bh / H, h = bh % H;
+  const int q0 = qb * BQ;
+  const int nblk = qb + 1;                          // causal: key blocks 0..qb
+  const int row_base = b * Tn;                      // row of token 0 of this batch in [B*T, 3C]
+
+  if (dbg != nullptr && threadIdx.x == 0) {         // per-CTA trace: start ns, end ns, SM id
+    unsigned long long t; unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    long long* rec3 = dbg + 1024 + 3 * (blockIdx.y * gridDim.x + blockIdx.x);
+    rec3[0] = static_cast<long long>(t);
+    rec3[2] = smid;
+  }
+  if (threadIdx.x == 0) {
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+    ptx::prefetch_tmap(&tmap_qkv);
+    ptx::mbar_init(q_full, 1);
+    for (int s = 0; s < KV_STAGES; ++s) { ptx::mbar_init(&kv_full[s], 1); ptx::mbar_init(&kv_empty[s], 1); }
+    ptx::mbar_init(s_full, 1);
+    ptx::mbar_init(p_full, 4);
+    ptx::mbar_init(o_full, 1);
+    ptx::mbar_init(pv_done, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(q_full, TILE);
+      ptx::tma_load_2d(sQ, &tmap_qkv, q_full, h * HD, row_base + q0);
+      for (int j = 0; j < nblk; ++j) {
+        const int s = j % KV_STAGES;
+        ptx::mbar_wait(&kv_empty[s], ((j / KV_STAGES) & 1) ^ 1);
+        ptx::mbar_expect_tx(&kv_full[s], 2 * TILE);
+        ptx::tma_load_2d(sKV + s * 2 * TILE, &tmap_qkv, &kv_full[s], C + h * HD, row_base + j * BKV);
+        ptx::tma_load_2d(sKV + s * 2 * TILE + TILE, &tmap_qkv, &kv_full[s], 2 * C + h * HD, row_base + j * BKV);
+      }
+    }
+  } else if (warp == 1) {
+    // MMA issuer: the warp stays converged, one elected lane issues (see ptx::elect_one)
+    {
+      constexpr uint32_t IDESC_S = ptx::umma_idesc_bf16(BQ, BKV, false, false);
+      constexpr uint32_t IDESC_O = ptx::umma_idesc_bf16(BQ, HD, false, true);   // B = V, MN-major
+      const bool rec = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+      // descriptors: only the 14-bit start-address field changes between MMAs
+      const uint64_t q_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(sQ), 16, 1024);
+      const uint64_t p_desc0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(sP), 16, 1024);
+      const uint64_t k_desc0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(sKV), 16, 1024);
+      const uint64_t v_desc0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(sKV + TILE), 64 * BKV * 2, 1024);
+      auto issue_s = [&](int jj) {                 // S = Q K_jj^T
+        const uint64_t k_desc = k_desc0 + static_cast<uint64_t>(((jj % KV_STAGES) * 2 * TILE) >> 4);
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k)
+            ptx::umma_bf16(tmem + S_COL, q_desc + static_cast<uint64_t>(2 * k), k_desc + static_cast<uint64_t>(2 * k),
+                           IDESC_S, k > 0 ? 1u : 0u);
+          ptx::umma_commit(s_full);
+        }
+        __syncwarp();
+      };
+      ptx::mbar_wait(q_full, 0);
+      ptx::mbar_wait(&kv_full[0], 0);
+      ptx::tc_fence_after();
+      issue_s(0);
+      for (int j = 0; j < nblk; ++j) {
+        const int s = j % KV_STAGES;
+        if (rec) dbg[512 + 4 * j] = clock64();
+        ptx::mbar_wait(p_full, j & 1);              // P_j in smem, S consumed, O rescaled if needed
+        ptx::tc_fence_after();
+        if (rec) dbg[512 + 4 * j + 1] = clock64();
+        if (j + 1 < nblk) {                         // next S first: the softmax warps wait for it
+          ptx::mbar_wait(&kv_full[(j + 1) % KV_STAGES], ((j + 1) / KV_STAGES) & 1);
+          ptx::tc_fence_after();
+          issue_s(j + 1);
+        }
+        if (rec) dbg[512 + 4 * j + 2] = clock64();
+        // O += P_j V_j.  P: K-major, two 64-column atoms of 16 KB; V: MN-major, 16 key rows = 2048 B / step
+        const uint64_t v_desc = v_desc0 + static_cast<uint64_t>((s * 2 * TILE) >> 4);
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int k = 0; k < BKV / 16; ++k)
+            ptx::umma_bf16(tmem + O_COL, p_desc0 + static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4),
+                           v_desc + static_cast<uint64_t>(128 * k), IDESC_O, (j > 0 || k > 0) ? 1u : 0u);
+          ptx::umma_commit(pv_done);                // P smem may be overwritten
+          ptx::umma_commit(&kv_empty[s]);           // K/V stage may be refilled
+          if (j == nblk - 1) ptx::umma_commit(o_full);
+        }
+        __syncwarp();
+        if (rec) dbg[512 + 4 * j + 3] = clock64();
+      }
+    }
+  } else {
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;                 // query row within the tile = TMEM lane
+    const int qi = q0 + row;
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    float m = -INFINITY, l = 0.f;
+    const uint32_t s_addr = tmem + lane_addr + S_COL, o_addr = tmem + lane_addr + O_COL;
+    const bool rec = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;
+    for (int j = 0; j < nblk; ++j) {
+      // S_j is ready; P V of block j-1 may still be running (pv_done is awaited before P is overwritten)
+      if (rec) dbg[4 * j] = clock64();
+      ptx::mbar_wait(s_full, j & 1);
+      ptx::tc_fence_after();
+      if (rec) dbg[4 * j + 1] = clock64();
+      uint64_t* pvb = j > 0 ? pv_done : nullptr;
+      const uint32_t pvp = static_cast<uint32_t>((j - 1) & 1);
+      const float corr = (j == qb) ? softmax_block<true>(s_addr, sP, row, qi - j * BKV, scale_log2, m, l, j == 0, pvb, pvp)
+                                   : softmax_block<false>(s_addr, sP, row, 0, scale_log2, m, l, j == 0, pvb, pvp);
+      if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+        // rare: this warp's rows rescale their O accumulator in TMEM (warp-uniform branch)
+        float v[32];
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          ptx::tmem_ld_32x32(o_addr + c * 32, v);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] *= corr;
+          ptx::tmem_st_32x32(o_addr + c * 32, v);
+        }
+      }
+      if (rec) dbg[4 * j + 2] = clock64();
+      ptx::fence_proxy_async();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(p_full);
+      if (rec) dbg[4 * j + 3] = clock64();
+    }
+    ptx::mbar_wait(o_full, 0);
+    ptx::tc_fence_after();
+    {
+      const float inv = 1.f / l;
+      const bool live = qi < Tn;                     // TMEM loads stay warp-collective; stores are predicated
+      uint4* dst = reinterpret_cast<uint4*>(y + (static_cast<size_t>(row_base) + (live ? qi : 0)) * C + h * HD);
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        float o[32];
+        ptx::tmem_ld_32x32(o_addr + c * 32, o);
+        if (live) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            dst[c * 4 + i] = make_uint4(pack_bf16x2(o[8 * i] * inv, o[8 * i + 1] * inv), pack_bf16x2(o[8 * i + 2] * inv, o[8 * i + 3] * inv),
+                                        pack_bf16x2(o[8 * i + 4] * inv, o[8 * i + 5] * inv), pack_bf16x2(o[8 * i + 6] * inv, o[8 * i + 7] * inv));
+        }
+      }
+      if (live) lse[(static_cast<size_t>(b) * H + h) * Tn + qi] = (m + log2f(l)) * 0.69314718055994531f;
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem, TMEM_COLS);
+  if (dbg != nullptr && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    dbg[1024 + 3 * (blockIdx.y * gridDim.x + blockIdx.x) + 1] = static_cast<long long>(t);
+  }
+}
+
+static long long* g_attn_dbg = nullptr;
+void attention_tc_set_debug_buffer(long long* p) { g_attn_dbg = p; }
+
+int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, int H, cudaStream_t stream) {
+  using namespace fatc;
+  const int C = H * HD;
+  CUtensorMap tm;
+  int rc = make_tmap_2d(&tm, qkv, 2, static_cast<uint64_t>(3) * C, static_cast<uint64_t>(B) * T,
+                        static_cast<uint64_t>(3) * C, HD, BQ);
+  if (rc) return rc;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    NSB_REQUIRE(e == cudaSuccess, "attention_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    attr_done = true;
+  }
+  const dim3 grid(B * H, (T + BQ - 1) / BQ);
+  attn_fwd_tc_kernel<<<grid, 192, SMEM_BYTES, stream>>>(tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
+                                                        1.4426950408889634f / sqrtf(static_cast<float>(HD)), g_attn_dbg);
+  count_launch();
+  return check_launch("attention_fwd_tc");
+}
+
+}  // namespace nsb

@@ -271,7 +271,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ============================================
-    if (lane == 0) {
+    // The whole warp walks the loop (converged); one elected lane issues the MMAs and commits.
+    {
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -294,16 +295,19 @@ __global__ void __launch_bounds__(kThreads, 1)
                                        : ptx::umma_smem_desc_sw128(a_addr, 16, 1024);
           const uint64_t b_desc = B_MN ? ptx::umma_smem_desc_sw128(b_addr, 64 * BK * 2, 1024)
                                        : ptx::umma_smem_desc_sw128(b_addr, 16, 1024);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t a_k = a_desc + static_cast<uint64_t>(A_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
-            const uint64_t b_k = b_desc + static_cast<uint64_t>(B_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
-            ptx::umma_bf16(d_tmem, a_k, b_k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t a_k = a_desc + static_cast<uint64_t>(A_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
+              const uint64_t b_k = b_desc + static_cast<uint64_t>(B_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
+              ptx::umma_bf16(d_tmem, a_k, b_k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
+            ptx::umma_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
+            if (kb == kb1 - 1) ptx::umma_commit(&tfull[as]);  // accumulator complete -> epilogue
           }
-          ptx::umma_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
+          __syncwarp();
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit(&tfull[as]);       // accumulator complete -> epilogue
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }

@@ -322,6 +322,18 @@ def _attention_ref(qkv, B, T, H, D):
     return y.transpose(1, 2).contiguous().view(B, T, Cc)
 
 
+@pytest.mark.parametrize("path", [0, 2])
+@pytest.mark.parametrize("B,T,H", [(2, 128, 3), (1, 1024, 2), (3, 100, 2), (2, 384, 4), (2, 64, 2)])
+def test_attention_bf16_paths(path, B, T, H):
+    """tcgen05 forward (path 0) and the mma.sync flash kernels (path 2) against torch SDPA."""
+    lib = _lib.load()
+    lib.nsb_attention_debug_config(path)
+    try:
+        test_attention_fwd_bwd(torch.bfloat16, B, T, H, 64)
+    finally:
+        lib.nsb_attention_debug_config(0)
+
+
 @pytest.mark.parametrize("dt,B,T,H,D", [
     (torch.float32, 2, 64, 4, 32), (torch.float32, 2, 100, 2, 64),
     (torch.bfloat16, 2, 256, 6, 64), (torch.bfloat16, 1, 1024, 2, 64), (torch.bfloat16, 3, 100, 2, 64),
