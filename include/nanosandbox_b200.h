@@ -145,9 +145,12 @@ int nsb_gemm(const nsb_gemm_args* args, nsb_stream_t stream);
  * place, y is [B, T, H, D] (= [B, T, C]) ready for c_proj.  lse [B, H, T] is saved for backward. */
 int nsb_attention_fwd(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H,
                       int D, nsb_stream_t stream);
-/* K4': dqkv [B, T, 3, H, D] from dy; delta [B, H, T] is caller-provided scratch. */
+/* K4': dqkv [B, T, 3, H, D] from dy.  delta [B, H, T] is caller-provided scratch.  dq_acc is an
+ * fp32 [B*T, H*D] accumulator for the tensor-core (tcgen05) path, bf16 with D = 64: the key-block
+ * CTAs reduce their dQ contributions into it; it must be all zeros on entry and is zero again on
+ * return.  NULL selects the two-pass kernels that need no accumulator. */
 int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const float* lse,
-                      void* dqkv, float* delta, int dtype, int B, int T, int H, int D,
+                      void* dqkv, float* delta, float* dq_acc, int dtype, int B, int T, int H, int D,
                       nsb_stream_t stream);
 
 #ifdef __cplusplus

@@ -55,7 +55,7 @@ SIGNATURES = {
     "nsb_colsum": (_I, [_P, _I, _I, _P, _I, _I, _I, _P]),
     "nsb_gemm": (_I, [C.POINTER(GemmArgs), _P]),
     "nsb_attention_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
-    "nsb_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "nsb_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
 }
 # test / tuning hooks exported by the library but not part of the reference-facing surface
 DEBUG_SIGNATURES = {

@@ -548,6 +548,8 @@ __global__ void __launch_bounds__(128)
 namespace nsb {
 int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, int H, cudaStream_t stream);
 void attention_tc_set_debug_buffer(long long* p);
+int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
+                            float* delta, float* dq_acc, int B, int T, int H, cudaStream_t stream);
 }
 using namespace nsb;
 
@@ -588,10 +590,16 @@ int nsb_attention_fwd(const void* qkv, void* y, float* lse, int dtype, int B, in
 }
 
 int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
-                      float* delta, int dtype, int B, int T, int H, int D, nsb_stream_t stream) {
+                      float* delta, float* dq_acc, int dtype, int B, int T, int H, int D, nsb_stream_t stream) {
   NSB_REQUIRE(dtype == NSB_F32 || dtype == NSB_BF16, "attention_bwd: bad dtype %d", dtype);
   NSB_REQUIRE(D % 32 == 0 && D >= 32 && D <= 128, "attention_bwd: head dim %d unsupported (32/64/96/128)", D);
   if (B == 0 || T == 0) return 0;
+  if (dtype == NSB_BF16 && D == 64 && g_attn_force_simt == 0 && dq_acc != nullptr) {
+    NSB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(dy) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(dq_acc) & 15) == 0,
+                "attention_bwd: qkv/dy/dq_acc must be 16-byte aligned");
+    return attention_bwd_tc_launch(qkv, y, dy, lse, dqkv, delta, dq_acc, B, T, H, cs(stream));
+  }
   const float scale = 1.0f / sqrtf(static_cast<float>(D));
   const long long rows = static_cast<long long>(B) * H * T;
   const unsigned rgrid = static_cast<unsigned>((rows + 7) / 8);

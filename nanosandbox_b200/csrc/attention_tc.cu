@@ -328,4 +328,356 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
   return check_launch("attention_fwd_tc");
 }
 
+
+// =============================================================================================
+// Backward pass on the tensor cores.
+//
+// One CTA owns 128 keys of one (batch, head) and walks the query blocks at or below the diagonal.
+// Per query block (all MMAs are tcgen05, M = 128):
+//   S^T  = K Q^T          (keys x queries)            A = K,    B = Q     (both K-major)
+//   dP^T = V dO^T                                      A = V,    B = dO
+//   P^T  = exp2(S^T*scale - lse[q]),  dS^T = P^T o (dP^T - delta[q])      one thread per key row
+//   dV  += P^T dO                                      A = P^T (smem), B = dO read MN-major
+//   dK  += dS^T Q                                      A = dS^T (smem), B = Q read MN-major
+//   dQ   = dS K          (queries x d)                 A = dS^T read MN-major (the same smem tile,
+//                                                      transposed by the descriptor), B = K MN-major
+// dV and dK accumulate in TMEM over the whole loop; dQ of the block goes TMEM -> swizzled smem ->
+// TMA reduce-add into an fp32 accumulator [B*T, C] shared by all key blocks (converted to bf16,
+// and re-zeroed, by attn_dq_convert_kernel).  Warps: 0 = TMA, 1 = MMA issue, 2..9 = two compute
+// groups, each taking 64 of the 128 query columns of every row.
+// =============================================================================================
+namespace fabw {
+constexpr int BQ = 128, BKV = 128, HD = 64;
+constexpr int TILE = 128 * 128;            // 16 KB: 128 rows x 128 B
+constexpr int OFF_K = 0, OFF_V = TILE, OFF_Q = 2 * TILE, OFF_DO = 4 * TILE;   // Q, dO: 2 stages each
+constexpr int OFF_PT = 6 * TILE, OFF_DS = 8 * TILE, OFF_DQ = 10 * TILE;       // 32 KB each
+constexpr int OFF_STAT = 12 * TILE;        // [2 stages][lse_log2 | delta][128] floats
+constexpr int OFF_BAR = OFF_STAT + 2 * 2 * 128 * 4;
+constexpr int SMEM_BYTES = OFF_BAR + 256;
+constexpr uint32_t TMEM_COLS = 512;
+constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
+}  // namespace fabw
+
+__global__ void __launch_bounds__(320, 1)
+    attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_dy,
+                       const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse,
+                       const float* __restrict__ delta, __nv_bfloat16* __restrict__ dqkv, int Tn, int H,
+                       float scale, float scale_log2) {
+  using namespace fabw;
+  using fatc::ex2;
+  using fatc::sw128;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* kv_full = bars;          // K, V landed
+  uint64_t* qdo_full = bars + 1;     // [2] Q_i, dO_i landed
+  uint64_t* qdo_empty = bars + 3;    // [2]
+  uint64_t* sdp_full = bars + 5;     // S^T, dP^T in TMEM
+  uint64_t* pds_full = bars + 6;     // P^T, dS^T in smem (and S^T/dP^T consumed)      count 8
+  uint64_t* dq_full = bars + 7;      // dV/dK/dQ MMAs of the block retired
+  uint64_t* dq_free = bars + 8;      // dQ columns read back                          count 8
+  uint64_t* dkv_full = bars + 9;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  float* stat = reinterpret_cast<float*>(smem + OFF_STAT);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int C = H * HD;
+  const int jb = blockIdx.y;                       // key block; block 0 has the longest loop and starts first
+  const int bh = blockIdx.x, b = bh / H, h = bh % H;
+  const int nq = (Tn + BQ - 1) / BQ;
+  const int nit = nq - jb;                         // query blocks jb .. nq-1
+  const int row_base = b * Tn;
+
+  if (threadIdx.x == 0) {
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+    ptx::prefetch_tmap(&tmap_qkv);
+    ptx::prefetch_tmap(&tmap_dy);
+    ptx::prefetch_tmap(&tmap_dq);
+    ptx::mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&qdo_full[s], 1); ptx::mbar_init(&qdo_empty[s], 1); }
+    ptx::mbar_init(sdp_full, 1);
+    ptx::mbar_init(pds_full, 8);
+    ptx::mbar_init(dq_full, 1);
+    ptx::mbar_init(dq_free, 8);
+    ptx::mbar_init(dkv_full, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(kv_full, 2 * TILE);
+      ptx::tma_load_2d(smem + OFF_K, &tmap_qkv, kv_full, C + h * HD, row_base + jb * BKV);
+      ptx::tma_load_2d(smem + OFF_V, &tmap_qkv, kv_full, 2 * C + h * HD, row_base + jb * BKV);
+      for (int it = 0; it < nit; ++it) {
+        const int s = it & 1;
+        ptx::mbar_wait(&qdo_empty[s], ((it >> 1) & 1) ^ 1);
+        ptx::mbar_expect_tx(&qdo_full[s], 2 * TILE);
+        ptx::tma_load_2d(smem + OFF_Q + s * TILE, &tmap_qkv, &qdo_full[s], h * HD, row_base + (jb + it) * BQ);
+        ptx::tma_load_2d(smem + OFF_DO + s * TILE, &tmap_dy, &qdo_full[s], h * HD, row_base + (jb + it) * BQ);
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t ID_SDP = ptx::umma_idesc_bf16(128, 128, false, false);  // S^T, dP^T
+    constexpr uint32_t ID_DKV = ptx::umma_idesc_bf16(128, 64, false, true);    // dV, dK: B MN-major
+    constexpr uint32_t ID_DQ = ptx::umma_idesc_bf16(128, 64, true, true);      // dQ: A and B MN-major
+    const uint32_t sb = ptx::smem_u32(smem);
+    const uint64_t dK_ = ptx::umma_smem_desc_sw128(sb + OFF_K, 16, 1024);            // A, K-major
+    const uint64_t dV_ = ptx::umma_smem_desc_sw128(sb + OFF_V, 16, 1024);
+    const uint64_t dKmn = ptx::umma_smem_desc_sw128(sb + OFF_K, TILE, 1024);         // B, MN-major (N = d)
+    const uint64_t dPT = ptx::umma_smem_desc_sw128(sb + OFF_PT, 16, 1024);           // A, K-major (K = q)
+    const uint64_t dDS = ptx::umma_smem_desc_sw128(sb + OFF_DS, 16, 1024);
+    const uint64_t dDSmn = ptx::umma_smem_desc_sw128(sb + OFF_DS, TILE, 1024);       // A, MN-major (M = q), LBO = next 64 q
+    auto issue_sdp = [&](int it) {
+      const int s = it & 1;
+      const uint64_t q_k = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, 16, 1024);
+      const uint64_t do_k = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, 16, 1024);
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tmem + C_S, dK_ + static_cast<uint64_t>(2 * k), q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tmem + C_DP, dV_ + static_cast<uint64_t>(2 * k), do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+        ptx::umma_commit(sdp_full);
+      }
+      __syncwarp();
+    };
+    ptx::mbar_wait(kv_full, 0);
+    ptx::mbar_wait(&qdo_full[0], 0);
+    ptx::tc_fence_after();
+    issue_sdp(0);
+    for (int it = 0; it < nit; ++it) {
+      const int s = it & 1;
+      ptx::mbar_wait(pds_full, it & 1);
+      ptx::tc_fence_after();
+      if (it + 1 < nit) {
+        ptx::mbar_wait(&qdo_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
+        ptx::tc_fence_after();
+        issue_sdp(it + 1);
+      }
+      const uint64_t q_mn = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, TILE, 1024);   // B MN-major (N = d, K = q)
+      const uint64_t do_mn = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, TILE, 1024);
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // K = 128 queries: A atom k/4, 32 B per step inside; B 16 q rows = 2048 B per step
+          const uint64_t a_off = static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4);
+          ptx::umma_bf16(tmem + C_DV, dPT + a_off, do_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint64_t a_off = static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4);
+          ptx::umma_bf16(tmem + C_DK, dDS + a_off, q_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+        }
+      }
+      __syncwarp();
+      if (it > 0) { ptx::mbar_wait(dq_free, (it - 1) & 1); ptx::tc_fence_after(); }
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)    // K = 128 keys: 16 key rows = 2048 B per step for both operands
+          ptx::umma_bf16(tmem + C_DQ, dDSmn + static_cast<uint64_t>(128 * k), dKmn + static_cast<uint64_t>(128 * k), ID_DQ, k > 0);
+        ptx::umma_commit(dq_full);
+        ptx::umma_commit(&qdo_empty[s]);
+        if (it == nit - 1) ptx::umma_commit(dkv_full);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int wg = (warp - 2) >> 2;                 // 0: query columns 0..63 of a block, 1: 64..127
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;                 // TMEM lane: key row (compute) / query row (dQ write-back)
+    const int et = (threadIdx.x - 64) & 127;
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    const int key = jb * BKV + row;
+    const float* lse_g = lse + (static_cast<size_t>(b) * H + h) * Tn;
+    const float* del_g = delta + (static_cast<size_t>(b) * H + h) * Tn;
+    const int ct = threadIdx.x - 64;                // 0..255: loader of the per-query statistics
+    auto load_stat = [&](int it) -> float {
+      const int qg = (jb + it) * BQ + (ct & 127);
+      if (qg >= Tn) return 0.f;
+      return ct < 128 ? lse_g[qg] * 1.4426950408889634f : del_g[qg];
+    };
+    auto writeback_dq = [&](int it) {               // dQ of query block (jb+it): TMEM -> smem -> reduce-add
+      float v[32];
+      ptx::tmem_ld_32x32(tmem + lane_addr + C_DQ + wg * 32, v);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(dq_free);
+      if (et == 0) ptx::bulk_wait_read<0>();        // the staging atom of this group is drained
+      ptx::named_bar_sync(1 + wg, 128);
+      uint8_t* stg = smem + OFF_DQ + wg * TILE;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<float4*>(stg + sw128(row, i)) =
+            make_float4(v[4 * i] * scale, v[4 * i + 1] * scale, v[4 * i + 2] * scale, v[4 * i + 3] * scale);
+      ptx::fence_proxy_async();
+      ptx::named_bar_sync(1 + wg, 128);
+      if (et == 0) {
+        ptx::tma_reduce_add_2d(&tmap_dq, stg, h * HD + wg * 32, row_base + (jb + it) * BQ);
+        ptx::bulk_commit();
+      }
+    };
+    float st_next = load_stat(0);
+    for (int it = 0; it < nit; ++it) {
+      // publish this block's statistics (prefetched one iteration ahead), fetch the next ones
+      stat[(it & 1) * 256 + ct] = st_next;
+      if (it + 1 < nit) st_next = load_stat(it + 1);
+      ptx::named_bar_sync(3, 256);
+      const float* lse2 = stat + (it & 1) * 256 + wg * 64;
+      const float* dlt = lse2 + 128;
+      const bool diag = (it == 0);
+      const int qlim = Tn - (jb + it) * BQ;         // query columns >= qlim are padding
+      ptx::mbar_wait(sdp_full, it & 1);
+      ptx::tc_fence_after();
+      uint32_t pk[32], dk[32];                      // packed bf16 pairs of P^T and dS^T (64 columns)
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float sv[32], dv[32];
+        ptx::tmem_ld_32x32_async(tmem + lane_addr + C_S + wg * 64 + c * 32, sv);
+        ptx::tmem_ld_32x32_async(tmem + lane_addr + C_DP + wg * 64 + c * 32, dv);
+        ptx::tmem_wait_ld32(sv);
+        ptx::tmem_wait_ld32(dv);
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const float4 l4 = *reinterpret_cast<const float4*>(lse2 + c * 32 + i);
+          const float4 d4 = *reinterpret_cast<const float4*>(dlt + c * 32 + i);
+          const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int col = wg * 64 + c * 32 + i + e;           // query column within the block
+            float p = ex2(fmaf(sv[i + e], scale_log2, -ls[e]));
+            const bool ok = (col < qlim) && (!diag || col >= row);
+            p = ok ? p : 0.f;
+            sv[i + e] = p;
+            dv[i + e] = p * (dv[i + e] - ds[e]);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          pk[c * 16 + i] = pack_bf16x2(sv[2 * i], sv[2 * i + 1]);
+          dk[c * 16 + i] = pack_bf16x2(dv[2 * i], dv[2 * i + 1]);
+        }
+      }
+      ptx::tc_fence_before();
+      // P^T / dS^T tiles are free once the previous block's dV/dK/dQ MMAs have retired
+      if (it > 0) ptx::mbar_wait(dq_full, (it - 1) & 1);
+      uint8_t* pt = smem + OFF_PT + wg * TILE;
+      uint8_t* dst = smem + OFF_DS + wg * TILE;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        *reinterpret_cast<uint4*>(pt + sw128(row, i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        *reinterpret_cast<uint4*>(dst + sw128(row, i)) = make_uint4(dk[4 * i], dk[4 * i + 1], dk[4 * i + 2], dk[4 * i + 3]);
+      }
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(pds_full);
+      if (it > 0) { ptx::tc_fence_after(); writeback_dq(it - 1); }
+    }
+    ptx::mbar_wait(dq_full, (nit - 1) & 1);
+    ptx::tc_fence_after();
+    writeback_dq(nit - 1);
+    // dK (group 0) / dV (group 1) of this key block
+    ptx::mbar_wait(dkv_full, 0);
+    ptx::tc_fence_after();
+    {
+      const bool live = key < Tn;
+      const float f = wg == 0 ? scale : 1.f;
+      __nv_bfloat16* out = dqkv + (static_cast<size_t>(row_base) + (live ? key : 0)) * (3 * C) + (wg == 0 ? C : 2 * C) + h * HD;
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        float v[32];
+        ptx::tmem_ld_32x32(tmem + lane_addr + (wg == 0 ? C_DK : C_DV) + c * 32, v);
+        if (live) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            reinterpret_cast<uint4*>(out)[c * 4 + i] =
+                make_uint4(pack_bf16x2(v[8 * i] * f, v[8 * i + 1] * f), pack_bf16x2(v[8 * i + 2] * f, v[8 * i + 3] * f),
+                           pack_bf16x2(v[8 * i + 4] * f, v[8 * i + 5] * f), pack_bf16x2(v[8 * i + 6] * f, v[8 * i + 7] * f));
+        }
+      }
+    }
+    if (et == 0) ptx::bulk_wait_all();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem, TMEM_COLS);
+}
+
+// dq (bf16, inside dqkv) = dq_acc (fp32); dq_acc is zeroed again for the next call
+__global__ void __launch_bounds__(256)
+    attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, size_t M, int C) {
+  const size_t i = (static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x) * 8;
+  if (i >= M * C) return;
+  const size_t r = i / C, c = i % C;
+  float4* src = reinterpret_cast<float4*>(dq_acc + i);
+  const float4 a = src[0], bq = src[1];
+  *reinterpret_cast<uint4*>(dqkv + r * 3 * C + c) =
+      make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(bq.x, bq.y), pack_bf16x2(bq.z, bq.w));
+  src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+  src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// delta[b,h,q] = sum_d dy*y : 8 threads per (row, head), 16-byte loads
+__global__ void __launch_bounds__(256)
+    attn_delta_tc_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy,
+                         float* __restrict__ delta, int B, int Tn, int H) {
+  const size_t g = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+  const size_t item = g >> 3;                       // (b*T + q) * H + h
+  const int part = static_cast<int>(g & 7);
+  const size_t total = static_cast<size_t>(B) * Tn * H;
+  float s = 0.f;
+  if (item < total) {
+    const uint4 a = *reinterpret_cast<const uint4*>(y + item * 64 + part * 8);
+    const uint4 d = *reinterpret_cast<const uint4*>(dy + item * 64 + part * 8);
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, dw[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 p = unpack_bf16x2(aw[k]), q = unpack_bf16x2(dw[k]);
+      s += p.x * q.x + p.y * q.y;
+    }
+  }
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  if (item < total && part == 0) {
+    const size_t bt = item / H, h = item % H;
+    const size_t b = bt / Tn, q = bt % Tn;
+    delta[(b * H + h) * Tn + q] = s;
+  }
+}
+
+int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
+                            float* delta, float* dq_acc, int B, int T, int H, cudaStream_t stream) {
+  using namespace fabw;
+  const int C = H * HD;
+  const uint64_t rows = static_cast<uint64_t>(B) * T;
+  CUtensorMap tq, tdy, tdq;
+  int rc = make_tmap_2d(&tq, qkv, 2, static_cast<uint64_t>(3) * C, rows, static_cast<uint64_t>(3) * C, HD, 128);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tdy, dy, 2, C, rows, C, HD, 128);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tdq, dq_acc, 4, C, rows, C, 32, 128);
+  if (rc) return rc;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    NSB_REQUIRE(e == cudaSuccess, "attention_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    attr_done = true;
+  }
+  const size_t items = rows * H * 8;
+  attn_delta_tc_kernel<<<static_cast<unsigned>((items + 255) / 256), 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H);
+  const dim3 grid(B * H, (T + BKV - 1) / BKV);
+  const float scale = 1.0f / sqrtf(static_cast<float>(HD));
+  attn_bwd_tc_kernel<<<grid, 320, SMEM_BYTES, stream>>>(tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
+                                                        scale, scale * 1.4426950408889634f);
+  const size_t n8 = rows * C / 8;
+  attn_dq_convert_kernel<<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, stream>>>(dq_acc, static_cast<__nv_bfloat16*>(dqkv), rows, C);
+  count_launch(3);
+  return check_launch("attention_bwd_tc");
+}
+
 }  // namespace nsb

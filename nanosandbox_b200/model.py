@@ -126,6 +126,8 @@ class _Acts:
         self.datt = new(M, C)
         self.dqkv = new(M, 3 * C)
         self.delta = new(B, H, T, dtype=f32)
+        # fp32 dQ accumulator of the tensor-core attention backward (kept all-zero between calls)
+        self.dq_acc = torch.zeros(M, C, dtype=f32, device=device) if (lowp and C // H == 64) else None
         self.ln_scratch = torch.empty(ops.layernorm_bwd_scratch_bytes(M, C) // 4, dtype=f32, device=device)
         self.idx = None
         self.targets = None
@@ -426,7 +428,7 @@ class GPT(nn.Module):
             # attention
             wgrad(dres_a, C, a.att[l], C, pre + "attn.c_proj", C, C)
             ops.gemm(M, C, C, dres_a, C, True, W(pre + "attn.c_proj.weight"), C, False, a.datt, C, EPI_STORE, stream=st)
-            ops.attention_bwd(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D, st)
+            ops.attention_bwd(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D, a.dq_acc, st)
             wgrad(a.dqkv, 3 * C, a.ln1[l], C, pre + "attn.c_attn", 3 * C, C)
             ops.gemm(M, C, 3 * C, a.dqkv, 3 * C, True, W(pre + "attn.c_attn.weight"), C, False, a.dln, C, EPI_STORE, stream=st)
             ops.layernorm_bwd(a.dln, a.x[l], P(pre + "ln_1.weight"), s[0], s[1], dres, a.dres[cur ^ 1],

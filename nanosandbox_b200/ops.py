@@ -142,9 +142,10 @@ def attention_fwd(qkv, y, lse, B, T, H, D, stream=None):
                                         B, T, H, D, stream or stream_handle()), "attention_fwd")
 
 
-def attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, stream=None):
+def attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc=None, stream=None):
+    """dq_acc: zero-filled fp32 [B*T, H*D] accumulator (tensor-core path) or None."""
     check(_lib.load().nsb_attention_bwd(qkv.data_ptr(), y.data_ptr(), dy.data_ptr(), lse.data_ptr(),
-                                        dqkv.data_ptr(), delta.data_ptr(), dtype_code(qkv), B, T, H, D,
+                                        dqkv.data_ptr(), delta.data_ptr(), ptr(dq_acc), dtype_code(qkv), B, T, H, D,
                                         stream or stream_handle()), "attention_bwd")
 
 

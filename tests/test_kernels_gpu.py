@@ -353,8 +353,11 @@ def test_attention_fwd_bwd(dt, B, T, H, D):
     ref.backward(dy.float())
     dqkv = torch.zeros_like(qkv)
     delta = torch.empty(B, H, T, device=DEV)
-    ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D)
+    dq_acc = torch.zeros(B * T, Cc, device=DEV) if (dt == torch.bfloat16 and D == 64) else None
+    ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc)
     torch.cuda.synchronize()
+    if dq_acc is not None:
+        assert not dq_acc.any()  # the accumulator is handed back zeroed
     g = ref_in.grad
     btol = 2e-5 if dt == torch.float32 else 2e-2
     assert_close(dqkv[..., :Cc], g[..., :Cc], btol, "dq")

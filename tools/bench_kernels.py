@@ -71,10 +71,11 @@ def main():
     lse = torch.empty(B, H, T, device=DEV)
     dqkv = torch.empty_like(qkv)
     delta = torch.empty(B, H, T, device=DEV)
+    dq_acc = torch.zeros(B * T, Cc, device=DEV)
     t = timeit(lambda: ops.attention_fwd(qkv, y, lse, B, T, H, D))
     fl = 4.0 * B * H * T * T * D / 2
     print(f"attention fwd  {t*1e3:8.1f} us {fl/t/1e9:7.1f} TF/s (causal flops)")
-    t = timeit(lambda: ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D))
+    t = timeit(lambda: ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc))
     print(f"attention bwd  {t*1e3:8.1f} us {2.5*fl/t/1e9:7.1f} TF/s (2.5x fwd flops)")
     q, k, v = [z.view(B, T, H, D).transpose(1, 2) for z in qkv.split(Cc, 2)]
     t = timeit(lambda: F.scaled_dot_product_attention(q, k, v, is_causal=True))

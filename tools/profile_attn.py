@@ -10,9 +10,10 @@ dy = torch.randn_like(y)
 lse = torch.empty(B, H, T, device="cuda")
 dqkv = torch.empty_like(qkv)
 delta = torch.empty(B, H, T, device="cuda")
+dq_acc = torch.zeros(B * T, C, device="cuda")
 for _ in range(3):
     ops.attention_fwd(qkv, y, lse, B, T, H, D)
     if "--bwd" in sys.argv:
-        ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D)
+        ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc)
 torch.cuda.synchronize()
 print("ok")
