@@ -30,8 +30,8 @@ constexpr int kMaxStages = 8;
 constexpr int kMaxBuf = 8;
 constexpr int STG_BYTES = 128 * 128;  // one epilogue staging buffer: 128 rows x 128 B (swizzled)
 constexpr size_t kSmemLimit = 232448;  // 227 KB opt-in maximum per CTA
-inline size_t smem_bytes_for(int bn, int stages, int nbuf) {
-  return static_cast<size_t>(stages) * (BM * BK * 2 + bn * BK * 2) + static_cast<size_t>(nbuf) * STG_BYTES +
+inline size_t smem_bytes_for(int bn_local, int stages, int nbuf) {  // bn_local: B rows staged per CTA
+  return static_cast<size_t>(stages) * (BM * BK * 2 + bn_local * BK * 2) + static_cast<size_t>(nbuf) * STG_BYTES +
          1024 /*align*/ + 256 /*barriers*/;
 }
 }  // namespace
@@ -184,15 +184,23 @@ __device__ __forceinline__ uint32_t stg_off(int row, int q) {  // 16-byte chunk 
   return static_cast<uint32_t>(row * 128 + ((q ^ (row & 7)) << 4));
 }
 
-template <int BN, bool A_MN, bool B_MN>
+// CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, cta_group::2) per 256 x BN
+// tile: each CTA stages its own 128 rows of A and its own half (BN/2 rows) of B, the leader issues
+// 256 x BN x 16 MMAs that read both CTAs' shared memory, each CTA keeps the accumulators of its 128
+// rows in its own TMEM and runs its own epilogue.  Halves the B traffic from L2 per CTA.
+template <int BN, bool A_MN, bool B_MN, int CG>
 __global__ void __launch_bounds__(kThreads, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                    const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
                    const __grid_constant__ CUtensorMap tma_aux, int K, int num_m, int num_n, int splits,
                    int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, EpiParams ep) {
-  constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
+  constexpr int BNL = BN / CG;                       // B rows staged by this CTA
+  constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BNL * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN;
-  constexpr uint32_t IDESC = ptx::umma_idesc_bf16(BM, BN, A_MN, B_MN);
+  constexpr uint32_t IDESC = ptx::umma_idesc_bf16(BM * CG, BN, A_MN, B_MN);
+  const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;
+  const int unit = static_cast<int>(blockIdx.x) / CG;      // CTA (CG=1) or pair (CG=2) index
+  const int nunits = static_cast<int>(gridDim.x) / CG;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -225,14 +233,18 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 4 * ngroups);
+      ptx::mbar_init(&tempty[s], 4 * ngroups * CG);   // epilogue warps of both CTAs release the leader
     }
     for (int s = 0; s < kMaxBuf; ++s) ptx::mbar_init(&auxfull[s], 1);
     ptx::fence_mbar_init();
   }
-  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 1) {
+    if (CG == 2) ptx::tmem_alloc_pair(tmem_slot, TMEM_COLS);
+    else ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  }
   ptx::tc_fence_before();
   __syncthreads();
+  if (CG == 2) ptx::cluster_sync();                   // peer barriers initialised before any remote signal
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -244,26 +256,33 @@ __global__ void __launch_bounds__(kThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       constexpr int A_BOXES = A_MN ? BM / 64 : 1;
-      constexpr int B_BOXES = B_MN ? BN / 64 : 1;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      constexpr int B_BOXES = B_MN ? BNL / 64 : 1;
+      for (int w = unit; w < total_work; w += nunits) {
         const TileCoord t = tile_of(w, num_m, num_n);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
+        const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
+        const int n0 = t.n_blk * BN + static_cast<int>(rank) * BNL;
         for (int kb = kb0; kb < kb1; ++kb) {
           if (lane == 0) {
             ptx::mbar_wait(&empty[stage], phase ^ 1);
-            ptx::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+            // the leader's barrier collects the bytes of both CTAs of a pair
+            if (rank == 0) ptx::mbar_expect_tx(&full[stage], (A_BYTES + B_BYTES) * CG);
           }
           __syncwarp();
           uint8_t* a_dst = smem_a + stage * A_BYTES;
           uint8_t* b_dst = smem_b + stage * B_BYTES;
           if (lane < A_BOXES) {
-            if (A_MN) ptx::tma_load_2d(a_dst + lane * (64 * BK * 2), &tma_a, &full[stage], t.m_blk * BM + lane * 64, kb * BK);
-            else ptx::tma_load_2d(a_dst, &tma_a, &full[stage], kb * BK, t.m_blk * BM);
+            void* dst = A_MN ? a_dst + lane * (64 * BK * 2) : a_dst;
+            const int c0 = A_MN ? m0 + lane * 64 : kb * BK, c1 = A_MN ? kb * BK : m0;
+            if (CG == 2) ptx::tma_load_2d_pair(dst, &tma_a, &full[stage], c0, c1);
+            else ptx::tma_load_2d(dst, &tma_a, &full[stage], c0, c1);
           } else if (lane < A_BOXES + B_BOXES) {
             const int j = lane - A_BOXES;
-            if (B_MN) ptx::tma_load_2d(b_dst + j * (64 * BK * 2), &tma_b, &full[stage], t.n_blk * BN + j * 64, kb * BK);
-            else ptx::tma_load_2d(b_dst, &tma_b, &full[stage], kb * BK, t.n_blk * BN);
+            void* dst = B_MN ? b_dst + j * (64 * BK * 2) : b_dst;
+            const int c0 = B_MN ? n0 + j * 64 : kb * BK, c1 = B_MN ? kb * BK : n0;
+            if (CG == 2) ptx::tma_load_2d_pair(dst, &tma_b, &full[stage], c0, c1);
+            else ptx::tma_load_2d(dst, &tma_b, &full[stage], c0, c1);
           }
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
@@ -272,12 +291,13 @@ __global__ void __launch_bounds__(kThreads, 1)
   } else if (warp == 1) {
     // ================================ MMA issuer ============================================
     // The whole warp walks the loop (converged); one elected lane issues the MMAs and commits.
-    {
+    // In a CTA pair only the leader issues; its commits arrive on the barriers of both CTAs.
+    if (rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      for (int w = unit; w < total_work; w += nunits) {
         const TileCoord t = tile_of(w, num_m, num_n);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
@@ -300,10 +320,16 @@ __global__ void __launch_bounds__(kThreads, 1)
             for (int k = 0; k < BK / 16; ++k) {
               const uint64_t a_k = a_desc + static_cast<uint64_t>(A_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
               const uint64_t b_k = b_desc + static_cast<uint64_t>(B_MN ? (k * 16 * 128) >> 4 : (k * 32) >> 4);
-              ptx::umma_bf16(d_tmem, a_k, b_k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+              if (CG == 2) ptx::umma_bf16_pair(d_tmem, a_k, b_k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+              else ptx::umma_bf16(d_tmem, a_k, b_k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
             }
-            ptx::umma_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
-            if (kb == kb1 - 1) ptx::umma_commit(&tfull[as]);  // accumulator complete -> epilogue
+            if (CG == 2) {
+              ptx::umma_commit_pair(&empty[stage]);
+              if (kb == kb1 - 1) ptx::umma_commit_pair(&tfull[as]);
+            } else {
+              ptx::umma_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
+              if (kb == kb1 - 1) ptx::umma_commit(&tfull[as]);  // accumulator complete -> epilogue
+            }
           }
           __syncwarp();
           if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -327,7 +353,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     } else if (!tma_epi) {
       // ---- direct-store fallback (outputs whose row stride is not a multiple of 16 bytes) ----
       const bool use_atomics = (ep.kind == NSB_EPI_ACCUM) && splits > 1;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      for (int w = unit; w < total_work; w += nunits) {
         const TileCoord t = tile_of(w, num_m, num_n);
         ptx::mbar_wait(&tfull[as], aphase);
         ptx::tc_fence_after();
@@ -335,11 +361,11 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int c = grp; c < BN / 32; c += ngroups) {
           float v[32];
           ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN + c * 32), v);
-          epilogue_row32(ep, t.m_blk * BM + row, t.n_blk * BN + c * 32, v, alpha, use_atomics);
+          epilogue_row32(ep, (t.m_blk * CG + static_cast<int>(rank)) * BM + row, t.n_blk * BN + c * 32, v, alpha, use_atomics);
         }
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&tempty[as]);
+        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     } else {
@@ -351,7 +377,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       const bool aux_tma = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU) && !aux_direct;
       const bool reduce = (ep.kind == NSB_EPI_ACCUM) && (ep.accumulate || splits > 1);
       const bool has_bias = ep.bias != nullptr && ep.kind != NSB_EPI_ACCUM && ep.kind != NSB_EPI_DGELU;
-      const int my_tiles = (total_work - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+      const int my_tiles = (total_work - unit + nunits - 1) / nunits;
       const int total_chunks = my_tiles * CHG;
       uint8_t* pool = smem_stg + grp * nbuf * STG_BYTES;
       uint64_t* auxbar = auxfull + grp * nbuf;
@@ -361,11 +387,11 @@ __global__ void __launch_bounds__(kThreads, 1)
       auto prefetch_aux = [&](int upto) {   // elected thread only
         while (next_aux <= upto && next_aux < total_chunks) {
           const int j = next_aux++;
-          const TileCoord t = tile_of(static_cast<int>(blockIdx.x) + (j / CHG) * static_cast<int>(gridDim.x), num_m, num_n);
+          const TileCoord t = tile_of(unit + (j / CHG) * nunits, num_m, num_n);
           const int b = j % nbuf;
           ptx::mbar_expect_tx(&auxbar[b], STG_BYTES);
           ptx::tma_load_2d(pool + b * STG_BYTES, &tma_aux, &auxbar[b],
-                           t.n_blk * BN + ((j % CHG) * ngroups + grp) * CW, t.m_blk * BM);
+                           t.n_blk * BN + ((j % CHG) * ngroups + grp) * CW, (t.m_blk * CG + static_cast<int>(rank)) * BM);
         }
       };
       // make the staged data visible to the async proxy, wait until the buffer about to be
@@ -384,11 +410,11 @@ __global__ void __launch_bounds__(kThreads, 1)
       };
       if (aux_tma && et == 0) prefetch_aux(nbuf - 1);
       int g = 0;                            // group-local chunk counter (aux kinds: emit == g)
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      for (int w = unit; w < total_work; w += nunits) {
         const TileCoord t = tile_of(w, num_m, num_n);
         ptx::mbar_wait(&tfull[as], aphase);
         ptx::tc_fence_after();
-        const int m0 = t.m_blk * BM;
+        const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
 #pragma unroll 1
         for (int c = grp; c < CH; c += ngroups, ++g) {
           const int n0 = t.n_blk * BN + c * CW;
@@ -500,7 +526,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&tempty[as]);
+        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
       if (et == 0) ptx::bulk_wait_all();
@@ -509,7 +535,11 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 1) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  if (CG == 2) ptx::cluster_sync();                   // the leader's MMAs read the peer's smem / TMEM until here
+  if (warp == 1) {
+    if (CG == 2) ptx::tmem_dealloc_pair(tmem_base, TMEM_COLS);
+    else ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
 }
 
 // ---- host: tensor maps --------------------------------------------------------------------------
@@ -585,32 +615,49 @@ struct LaunchPlan {
   int K, num_m, num_n, splits, kb_per_split, stages, nbuf, tma_epi, ngroups, aux_direct;
 };
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int CG>
 static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_t stream) {
-  auto kern = gemm_tc_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, CG>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemLimit));
     NSB_REQUIRE(e == cudaSuccess, "gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     attr_done = true;
   }
-  const size_t smem = smem_bytes_for(BN, lp.stages, lp.nbuf * lp.ngroups);
+  const size_t smem = smem_bytes_for(BN / CG, lp.stages, lp.nbuf * lp.ngroups);
   const int total = lp.num_m * lp.num_n * lp.splits;
-  const int grid = total < sm_count() ? total : sm_count();
-  kern<<<grid, kThreads, smem, stream>>>(lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
-                                          lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, ep);
+  const int units = sm_count() / CG;
+  const int grid = (total < units ? total : units) * CG;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
+                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, ep);
+  NSB_REQUIRE(e == cudaSuccess, "gemm_tc: launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("gemm_tc");
 }
 
 int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t stream, int force_bn, int force_splits,
-                   int force_direct_epi, int force_groups) {
+                   int force_direct_epi, int force_groups, int force_cg) {
   const int M = a->M, N = a->N, K = a->K;
   int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
   if (force_bn == 128 || force_bn == 256) bn = force_bn;
+  // CTA pairs (256-row tiles) for the wide-N tile whenever there are at least two 128-row blocks
+  int cg = (bn == 256 && M > 128) ? 2 : 1;
+  if (force_cg == 1 || (force_cg == 2 && bn == 256)) cg = force_cg;
   LaunchPlan lp;
   lp.K = K;
-  lp.num_m = (M + BM - 1) / BM;
+  lp.num_m = (M + BM * cg - 1) / (BM * cg);
   lp.num_n = (N + bn - 1) / bn;
   const int total_kb = (K + BK - 1) / BK;
   // split-K only where the epilogue can accumulate into a pre-existing fp32 C.  Pick the split that
@@ -618,7 +665,7 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   // than the number of splits for the short-and-wide weight-gradient shapes.
   int splits = 1;
   if (ep.kind == NSB_EPI_ACCUM && ep.accumulate) {
-    const int tiles = lp.num_m * lp.num_n, sms = sm_count();
+    const int tiles = lp.num_m * lp.num_n, sms = sm_count() / cg;
     if (tiles < 2 * sms) {
       double best = 1e30;
       const int max_splits = total_kb / 4 > 0 ? (total_kb / 4 < 32 ? total_kb / 4 : 32) : 1;
@@ -643,7 +690,7 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   if (a->a_kmajor) rc = make_tmap_2d(&lp.ta, a->A, 2, K, M, a->lda, BK, BM);
   else             rc = make_tmap_2d(&lp.ta, a->A, 2, M, K, a->lda, 64, BK);
   if (rc) return rc;
-  if (a->b_kmajor) rc = make_tmap_2d(&lp.tb, a->B, 2, K, N, a->ldb, BK, bn);
+  if (a->b_kmajor) rc = make_tmap_2d(&lp.tb, a->B, 2, K, N, a->ldb, BK, bn / cg);
   else             rc = make_tmap_2d(&lp.tb, a->B, 2, N, K, a->ldb, 64, BK);
   if (rc) return rc;
 
@@ -673,21 +720,26 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   lp.aux_direct = (ep.kind == NSB_EPI_DGELU && lp.ngroups == 2) ? 1 : 0;
   lp.nbuf = tma_epi ? ((has_aux && !lp.aux_direct) ? 4 : 2) : 0;
   int stages = kMaxStages;
-  while (stages > 2 && smem_bytes_for(bn, stages, lp.nbuf * lp.ngroups) > kSmemLimit) --stages;
+  while (stages > 2 && smem_bytes_for(bn / cg, stages, lp.nbuf * lp.ngroups) > kSmemLimit) --stages;
   lp.stages = stages;
 
-#define NSB_GEMM_CASE(BNV, AMN, BMN) return launch_variant<BNV, AMN, BMN>(lp, ep, stream)
+#define NSB_GEMM_CASE(BNV, AMN, BMN, CGV) return launch_variant<BNV, AMN, BMN, CGV>(lp, ep, stream)
   const bool amn = !a->a_kmajor, bmn = !a->b_kmajor;
-  if (bn == 256) {
-    if (!amn && !bmn) NSB_GEMM_CASE(256, false, false);
-    if (!amn && bmn) NSB_GEMM_CASE(256, false, true);
-    if (amn && !bmn) NSB_GEMM_CASE(256, true, false);
-    NSB_GEMM_CASE(256, true, true);
+  if (bn == 256 && cg == 2) {
+    if (!amn && !bmn) NSB_GEMM_CASE(256, false, false, 2);
+    if (!amn && bmn) NSB_GEMM_CASE(256, false, true, 2);
+    if (amn && !bmn) NSB_GEMM_CASE(256, true, false, 2);
+    NSB_GEMM_CASE(256, true, true, 2);
+  } else if (bn == 256) {
+    if (!amn && !bmn) NSB_GEMM_CASE(256, false, false, 1);
+    if (!amn && bmn) NSB_GEMM_CASE(256, false, true, 1);
+    if (amn && !bmn) NSB_GEMM_CASE(256, true, false, 1);
+    NSB_GEMM_CASE(256, true, true, 1);
   } else {
-    if (!amn && !bmn) NSB_GEMM_CASE(128, false, false);
-    if (!amn && bmn) NSB_GEMM_CASE(128, false, true);
-    if (amn && !bmn) NSB_GEMM_CASE(128, true, false);
-    NSB_GEMM_CASE(128, true, true);
+    if (!amn && !bmn) NSB_GEMM_CASE(128, false, false, 1);
+    if (!amn && bmn) NSB_GEMM_CASE(128, false, true, 1);
+    if (amn && !bmn) NSB_GEMM_CASE(128, true, false, 1);
+    NSB_GEMM_CASE(128, true, true, 1);
   }
 #undef NSB_GEMM_CASE
 }
@@ -698,7 +750,7 @@ int gemm_simt_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t s
 
 using namespace nsb;
 
-static int g_force_bn = 0, g_force_splits = 0, g_force_simt = 0, g_force_direct_epi = 0, g_force_groups = 0;
+static int g_force_bn = 0, g_force_splits = 0, g_force_simt = 0, g_force_direct_epi = 0, g_force_groups = 0, g_force_cg = 0;
 
 extern "C" {
 
@@ -711,6 +763,7 @@ void nsb_gemm_debug_config(int force_bn, int force_splits, int force_simt) {
   g_force_simt = force_simt == 1;
   g_force_direct_epi = force_simt == 2;
   g_force_groups = force_simt == 3 ? 1 : (force_simt == 4 ? 2 : 0);  // 3: one epilogue group, 4: two
+  g_force_cg = force_simt == 5 ? 1 : (force_simt == 6 ? 2 : 0);      // 5: single-CTA tiles, 6: CTA pairs
 }
 
 int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
@@ -727,7 +780,7 @@ int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
   ep.bias = a->bias; ep.alpha = a->alpha; ep.ldc = a->ldc; ep.c_bf16 = (a->c_dtype == NSB_BF16) ? 1 : 0;
   ep.accumulate = a->accumulate;
   if (a->in_dtype == NSB_F32 || g_force_simt) return gemm_simt_launch(a, ep, cs(stream));
-  return gemm_tc_launch(a, ep, cs(stream), g_force_bn, g_force_splits, g_force_direct_epi, g_force_groups);
+  return gemm_tc_launch(a, ep, cs(stream), g_force_bn, g_force_splits, g_force_direct_epi, g_force_groups, g_force_cg);
 }
 
 }  // extern "C"
