@@ -110,6 +110,43 @@ def cpu_reference_run(steps: int, warmup: int, micro_batch: int = 2):
     return tok_s, dt / steps * 1e3, cores, sample
 
 
+def torch_gpu_baseline(dev, micro_steps: int = 8):
+    """Informational: the SAME step on stock PyTorch CUDA ops (oracle model under bf16 autocast,
+    SDPA flash attention, cuBLAS, fused AdamW) on this GPU, for `micro_steps` micro-steps."""
+    from oracle.model import GPT as RefGPT, GPTConfig as RefConfig
+    torch.manual_seed(1337)
+    model = RefGPT(RefConfig(**CFG), verbose=False).to(dev)
+    opt = model.configure_optimizers(0.1, 6e-4, (0.9, 0.95), "cuda", verbose=False)
+    T, V = CFG["block_size"], CFG["vocab_size"]
+    x = torch.randint(0, V, (BATCH, T), device=dev)
+    y = torch.randint(0, V, (BATCH, T), device=dev)
+
+    def step():
+        for _ in range(micro_steps):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                _, loss = model(x, y)
+            (loss / micro_steps).backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(2):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 2
+    del model, opt
+    torch.cuda.empty_cache()
+    return {"value": micro_steps * BATCH * T / (ms / 1e3), "unit": "tokens/s",
+            "what": f"stock PyTorch {torch.__version__} eager (cuBLAS, SDPA, fused AdamW, bf16 autocast), same model, "
+                    f"{micro_steps} micro-steps per optimizer step, same GPU; informational, not the reference arm"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -134,6 +171,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--bucket-dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-torch-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -288,6 +326,15 @@ def main():
                 "nominal_GBps": 900.0, "bucket_dtype": args.bucket_dtype}
         model.buckets.time_comm = False
 
+    torch_gpu = None
+    if rank == 0 and world == 1 and not args.no_torch_baseline:
+        del resident
+        model = raw = opt = None
+        torch.cuda.empty_cache()
+        try:
+            torch_gpu = torch_gpu_baseline(dev)
+        except Exception as exc:  # informational only
+            torch_gpu = {"error": repr(exc)[:200]}
     if rank == 0:
         cpu = None
         if not args.no_cpu_baseline:
@@ -308,6 +355,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "torch_gpu_baseline": torch_gpu,
         }
         if comm is not None:
             line["allreduce"] = comm

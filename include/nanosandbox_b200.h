@@ -107,6 +107,11 @@ int nsb_adamw_step(float* p, const float* g, float* m, float* v, void* p_lowp,
 int nsb_cast_f32_to_bf16(const float* in, void* out, size_t n, float scale, nsb_stream_t stream);
 int nsb_cast_bf16_to_f32(const void* in, float* out, size_t n, nsb_stream_t stream);
 int nsb_scale_f32(float* x, size_t n, float scale, nsb_stream_t stream);
+/* Stand-alone exact-erf GELU on bf16 activations (nn.GELU(), torch/nn/modules/activation.py:777-808):
+ * a = gelu(h), and in place da <- da * gelu'(h).  The same math is also available fused into the
+ * GEMM epilogues (NSB_EPI_GELU / NSB_EPI_DGELU); on B200 the split form is faster for K = 768. */
+int nsb_gelu_fwd_bf16(const void* h, void* a, size_t n, nsb_stream_t stream);
+int nsb_gelu_bwd_bf16(void* da, const void* h, size_t n, nsb_stream_t stream);
 /* db[n] (+)= sum_m dy[m, n]  (bias gradients; autograd of F.linear's bias add) */
 int nsb_colsum(const void* dy, int dtype, int ld, float* db, int accumulate, int M, int N,
                nsb_stream_t stream);

@@ -52,6 +52,8 @@ SIGNATURES = {
     "nsb_cast_f32_to_bf16": (_I, [_P, _P, _Z, _F, _P]),
     "nsb_cast_bf16_to_f32": (_I, [_P, _P, _Z, _P]),
     "nsb_scale_f32": (_I, [_P, _Z, _F, _P]),
+    "nsb_gelu_fwd_bf16": (_I, [_P, _P, _Z, _P]),
+    "nsb_gelu_bwd_bf16": (_I, [_P, _P, _Z, _P]),
     "nsb_colsum": (_I, [_P, _I, _I, _P, _I, _I, _I, _P]),
     "nsb_gemm": (_I, [C.POINTER(GemmArgs), _P]),
     "nsb_attention_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
@@ -60,6 +62,7 @@ SIGNATURES = {
 # test / tuning hooks exported by the library but not part of the reference-facing surface
 DEBUG_SIGNATURES = {
     "nsb_gemm_debug_config": (None, [_I, _I, _I]),
+    "nsb_gemm_debug_timing": (None, [_P]),
     "nsb_attention_debug_config": (None, [_I]),
     "nsb_attention_debug_timing": (None, [_P]),
 }

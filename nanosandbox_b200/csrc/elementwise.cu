@@ -148,9 +148,11 @@ __global__ void __launch_bounds__(256)
 }
 
 // Stage 1 of the backward: dx (+ residual gradient) per row, per-CTA column partials of dw/db.
-// part layout: [gridDim.x][2][C]
-template <int NV, typename DyT>
-__global__ void __launch_bounds__(256)
+// part layout: [gridDim.x][2][C].  Register diet (3 CTAs of 8 warps per SM): only dy and x of the
+// row stay live between the two passes, xhat and dy*w are recomputed (w comes from L1), and the
+// db accumulators exist only when a bias gradient is wanted.
+template <int NV, typename DyT, bool HAS_DB>
+__global__ void __launch_bounds__(256, 3)
     layernorm_bwd_kernel(const DyT* __restrict__ dy, const float* __restrict__ x,
                          const float* __restrict__ w, const float* __restrict__ mean,
                          const float* __restrict__ rstd, const float* __restrict__ dres_in,
@@ -158,30 +160,39 @@ __global__ void __launch_bounds__(256)
                          float* __restrict__ part, int M, int C) {
   __shared__ float red[8][128 * NV];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float4 dwacc[NV], dbacc[NV];
+  float4 dwacc[NV], dbacc[HAS_DB ? NV : 1];
 #pragma unroll
-  for (int j = 0; j < NV; ++j) dwacc[j] = dbacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int j = 0; j < NV; ++j) dwacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < (HAS_DB ? NV : 1); ++j) dbacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
   const float invC = 1.0f / static_cast<float>(C);
 
   for (int row = blockIdx.x * 8 + warp; row < M; row += gridDim.x * 8) {
     const size_t off = static_cast<size_t>(row) * C;
     const float mu = mean[row], rs = rstd[row];
-    float4 g[NV], xh[NV];
+    float4 dyv[NV], xv[NV];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int c = (lane + 32 * j) * 4;
       if (c < C) {
-        const float4 d = Vec4IO<DyT>::load(dy + off + c);
-        const float4 xv = Vec4IO<float>::load(x + off + c);
+        dyv[j] = Vec4IO<DyT>::load(dy + off + c);
+        xv[j] = Vec4IO<float>::load(x + off + c);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int c = (lane + 32 * j) * 4;
+      if (c < C) {
         const float4 wv = __ldg(reinterpret_cast<const float4*>(w + c));
-        xh[j] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
-        g[j] = make_float4(d.x * wv.x, d.y * wv.y, d.z * wv.z, d.w * wv.w);
-        s1 += (g[j].x + g[j].y) + (g[j].z + g[j].w);
-        s2 += (g[j].x * xh[j].x + g[j].y * xh[j].y) + (g[j].z * xh[j].z + g[j].w * xh[j].w);
-        dwacc[j].x += d.x * xh[j].x; dwacc[j].y += d.y * xh[j].y;
-        dwacc[j].z += d.z * xh[j].z; dwacc[j].w += d.w * xh[j].w;
-        dbacc[j].x += d.x; dbacc[j].y += d.y; dbacc[j].z += d.z; dbacc[j].w += d.w;
+        const float4 d = dyv[j];
+        const float4 xh = make_float4((xv[j].x - mu) * rs, (xv[j].y - mu) * rs, (xv[j].z - mu) * rs, (xv[j].w - mu) * rs);
+        const float4 g = make_float4(d.x * wv.x, d.y * wv.y, d.z * wv.z, d.w * wv.w);
+        s1 += (g.x + g.y) + (g.z + g.w);
+        s2 += (g.x * xh.x + g.y * xh.y) + (g.z * xh.z + g.w * xh.w);
+        dwacc[j].x += d.x * xh.x; dwacc[j].y += d.y * xh.y;
+        dwacc[j].z += d.z * xh.z; dwacc[j].w += d.w * xh.w;
+        if (HAS_DB) { dbacc[j].x += d.x; dbacc[j].y += d.y; dbacc[j].z += d.z; dbacc[j].w += d.w; }
       }
     }
     const float c1 = warp_sum(s1) * invC, c2 = warp_sum(s2) * invC;
@@ -189,8 +200,11 @@ __global__ void __launch_bounds__(256)
     for (int j = 0; j < NV; ++j) {
       const int c = (lane + 32 * j) * 4;
       if (c < C) {
-        float4 o = make_float4(rs * (g[j].x - c1 - xh[j].x * c2), rs * (g[j].y - c1 - xh[j].y * c2),
-                               rs * (g[j].z - c1 - xh[j].z * c2), rs * (g[j].w - c1 - xh[j].w * c2));
+        const float4 wv = __ldg(reinterpret_cast<const float4*>(w + c));
+        const float4 d = dyv[j];
+        const float4 xh = make_float4((xv[j].x - mu) * rs, (xv[j].y - mu) * rs, (xv[j].z - mu) * rs, (xv[j].w - mu) * rs);
+        float4 o = make_float4(rs * (d.x * wv.x - c1 - xh.x * c2), rs * (d.y * wv.y - c1 - xh.y * c2),
+                               rs * (d.z * wv.z - c1 - xh.z * c2), rs * (d.w * wv.w - c1 - xh.w * c2));
         if (dres_in != nullptr) {
           const float4 r = Vec4IO<float>::load(dres_in + off + c);
           o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
@@ -202,12 +216,12 @@ __global__ void __launch_bounds__(256)
   }
   // cross-warp reduction of the column partials, dw then db
 #pragma unroll
-  for (int pass = 0; pass < 2; ++pass) {
+  for (int pass = 0; pass < (HAS_DB ? 2 : 1); ++pass) {
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int c = (lane + 32 * j) * 4;
-      const float4 a = pass == 0 ? dwacc[j] : dbacc[j];
+      const float4 a = (pass == 0 || !HAS_DB) ? dwacc[j] : dbacc[HAS_DB ? j : 0];
       *reinterpret_cast<float4*>(&red[warp][c]) = a;
     }
     __syncthreads();
@@ -537,6 +551,38 @@ __global__ void __launch_bounds__(256) scale_f32_kernel(float* __restrict__ x, s
   }
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) x[n4 * 4 + threadIdx.x] *= s;
 }
+// exact-erf GELU on bf16 activations (fp32 math inside), 8 elements per thread per step
+__global__ void __launch_bounds__(256)
+    gelu_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ h, __nv_bfloat16* __restrict__ a, size_t n8) {
+  for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n8; i += static_cast<size_t>(gridDim.x) * 256) {
+    const uint4 u = ld_stream(h + i * 8);
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 x = unpack_bf16x2(w[k]);
+      o[k] = pack_bf16x2(gelu_fast(x.x), gelu_fast(x.y));
+    }
+    st_stream(a + i * 8, make_uint4(o[0], o[1], o[2], o[3]));
+  }
+}
+// dh = dA * gelu'(h), in place over dA
+__global__ void __launch_bounds__(256)
+    gelu_bwd_bf16_kernel(__nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ h, size_t n8) {
+  for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n8; i += static_cast<size_t>(gridDim.x) * 256) {
+    const uint4 g = ld_stream(da + i * 8);
+    const uint4 u = ld_stream(h + i * 8);
+    const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, hw[4] = {u.x, u.y, u.z, u.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 x = unpack_bf16x2(hw[k]), d = unpack_bf16x2(gw[k]);
+      o[k] = pack_bf16x2(d.x * gelu_fast_grad(x.x), d.y * gelu_fast_grad(x.y));
+    }
+    st_stream(da + i * 8, make_uint4(o[0], o[1], o[2], o[3]));
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
     colsum_kernel(const T* __restrict__ dy, int ld, float* __restrict__ db, int accumulate, int M,
@@ -644,13 +690,13 @@ int nsb_layernorm_fwd(const float* x, const float* w, const float* b, void* y, i
 
 static inline int ln_bwd_grid(int M) {
   int g = (M + 7) / 8;
-  const int cap = 2 * sm_count();
+  const int cap = 3 * sm_count();  // 3 resident CTAs per SM; scratch contract: at most 4 x 160 slabs
   return g < cap ? (g < 1 ? 1 : g) : cap;
 }
 size_t nsb_layernorm_bwd_scratch_bytes(int M, int C) {
   (void)M;
   // sized for the largest grid the launcher may pick, independent of the device queried later
-  return static_cast<size_t>(2 * 160) * 2 * static_cast<size_t>(C) * sizeof(float);
+  return static_cast<size_t>(4 * 160) * 2 * static_cast<size_t>(C) * sizeof(float);
 }
 
 namespace nsb {
@@ -670,16 +716,14 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
   if (static_cast<size_t>(grid) * per_part > scratch_bytes) grid = static_cast<int>(scratch_bytes / per_part);
   NSB_REQUIRE(grid >= 1 && scratch != nullptr, "layernorm_bwd: scratch too small (%zu bytes)", scratch_bytes);
   const int nv = (C + 127) / 128;
+#define NSB_LN_BWD(TT, HASDB)                                                                  \
+  layernorm_bwd_kernel<NV, TT, HASDB><<<grid, 256, 0, stream>>>(                                \
+      static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx, static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C)
   NSB_LN_DISPATCH(nv, {
-    if (dy_dtype == NSB_F32)
-      layernorm_bwd_kernel<NV, float><<<grid, 256, 0, stream>>>(
-          static_cast<const float*>(dy), x, w, mean, rstd, dres_in, dx,
-          static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C);
-    else
-      layernorm_bwd_kernel<NV, __nv_bfloat16><<<grid, 256, 0, stream>>>(
-          static_cast<const __nv_bfloat16*>(dy), x, w, mean, rstd, dres_in, dx,
-          static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C);
+    if (dy_dtype == NSB_F32) { if (db != nullptr) NSB_LN_BWD(float, true); else NSB_LN_BWD(float, false); }
+    else { if (db != nullptr) NSB_LN_BWD(__nv_bfloat16, true); else NSB_LN_BWD(__nv_bfloat16, false); }
   });
+#undef NSB_LN_BWD
   layernorm_bwd_reduce_kernel<<<dim3((C + 31) / 32, 2), dim3(32, 8), 0, stream>>>(
       scratch, dw, db, grid, C, accumulate);
   count_launch(2);
@@ -804,6 +848,22 @@ int nsb_scale_f32(float* x, size_t n, float scale, nsb_stream_t stream) {
   scale_f32_kernel<<<grid_for(n / 4, 256 * 4, 8 * sm_count()), 256, 0, cs(stream)>>>(x, n, scale);
   count_launch();
   return check_launch("scale_f32");
+}
+int nsb_gelu_fwd_bf16(const void* h, void* a, size_t n, nsb_stream_t stream) {
+  NSB_REQUIRE(n % 8 == 0 && aligned16(h) && aligned16(a), "gelu_fwd_bf16: need 16-byte aligned buffers and n %% 8 == 0");
+  if (n == 0) return 0;
+  gelu_fwd_bf16_kernel<<<grid_for(n / 8, 256 * 2, 16 * sm_count()), 256, 0, cs(stream)>>>(
+      static_cast<const __nv_bfloat16*>(h), static_cast<__nv_bfloat16*>(a), n / 8);
+  count_launch();
+  return check_launch("gelu_fwd_bf16");
+}
+int nsb_gelu_bwd_bf16(void* da, const void* h, size_t n, nsb_stream_t stream) {
+  NSB_REQUIRE(n % 8 == 0 && aligned16(h) && aligned16(da), "gelu_bwd_bf16: need 16-byte aligned buffers and n %% 8 == 0");
+  if (n == 0) return 0;
+  gelu_bwd_bf16_kernel<<<grid_for(n / 8, 256 * 2, 16 * sm_count()), 256, 0, cs(stream)>>>(
+      static_cast<__nv_bfloat16*>(da), static_cast<const __nv_bfloat16*>(h), n / 8);
+  count_launch();
+  return check_launch("gelu_bwd_bf16");
 }
 int nsb_colsum(const void* dy, int dtype, int ld, float* db, int accumulate, int M, int N,
                nsb_stream_t stream) {

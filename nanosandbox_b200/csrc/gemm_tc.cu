@@ -25,14 +25,14 @@ namespace nsb {
 namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kThreads = 320;  // TMA warp, MMA warp, 2 x 4 epilogue warps
+
 constexpr int kMaxStages = 8;
 constexpr int kMaxBuf = 8;
 constexpr int STG_BYTES = 128 * 128;  // one epilogue staging buffer: 128 rows x 128 B (swizzled)
 constexpr size_t kSmemLimit = 232448;  // 227 KB opt-in maximum per CTA
 inline size_t smem_bytes_for(int bn_local, int stages, int nbuf) {  // bn_local: B rows staged per CTA
   return static_cast<size_t>(stages) * (BM * BK * 2 + bn_local * BK * 2) + static_cast<size_t>(nbuf) * STG_BYTES +
-         1024 /*align*/ + 256 /*barriers*/;
+         1024 /*align*/ + 512 /*barriers*/;
 }
 }  // namespace
 
@@ -101,7 +101,7 @@ __device__ __forceinline__ void epilogue_row32(const EpiParams& p, int m, int n,
         if (p.kind == NSB_EPI_GELU) {
           uint4* c2 = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.C2) + o);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_exact(round_bf16(v[j]));
+          for (int j = 0; j < 32; ++j) v[j] = gelu_fast(round_bf16(v[j]));
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             c2[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
@@ -144,14 +144,14 @@ __device__ __forceinline__ void epilogue_row32(const EpiParams& p, int m, int n,
           const uint4 u = h[j];
           const float2 h0 = unpack_bf16x2(u.x), h1 = unpack_bf16x2(u.y), h2 = unpack_bf16x2(u.z),
                        h3 = unpack_bf16x2(u.w);
-          c[j] = make_uint4(pack_bf16x2(round_bf16(v[8 * j]) * gelu_exact_grad(h0.x),
-                                        round_bf16(v[8 * j + 1]) * gelu_exact_grad(h0.y)),
-                            pack_bf16x2(round_bf16(v[8 * j + 2]) * gelu_exact_grad(h1.x),
-                                        round_bf16(v[8 * j + 3]) * gelu_exact_grad(h1.y)),
-                            pack_bf16x2(round_bf16(v[8 * j + 4]) * gelu_exact_grad(h2.x),
-                                        round_bf16(v[8 * j + 5]) * gelu_exact_grad(h2.y)),
-                            pack_bf16x2(round_bf16(v[8 * j + 6]) * gelu_exact_grad(h3.x),
-                                        round_bf16(v[8 * j + 7]) * gelu_exact_grad(h3.y)));
+          c[j] = make_uint4(pack_bf16x2(round_bf16(v[8 * j]) * gelu_fast_grad(h0.x),
+                                        round_bf16(v[8 * j + 1]) * gelu_fast_grad(h0.y)),
+                            pack_bf16x2(round_bf16(v[8 * j + 2]) * gelu_fast_grad(h1.x),
+                                        round_bf16(v[8 * j + 3]) * gelu_fast_grad(h1.y)),
+                            pack_bf16x2(round_bf16(v[8 * j + 4]) * gelu_fast_grad(h2.x),
+                                        round_bf16(v[8 * j + 5]) * gelu_fast_grad(h2.y)),
+                            pack_bf16x2(round_bf16(v[8 * j + 6]) * gelu_fast_grad(h3.x),
+                                        round_bf16(v[8 * j + 7]) * gelu_fast_grad(h3.y)));
         }
       } else {
         const float4* h = reinterpret_cast<const float4*>(static_cast<const float*>(p.aux) + o);
@@ -188,12 +188,15 @@ __device__ __forceinline__ uint32_t stg_off(int row, int q) {  // 16-byte chunk 
 // tile: each CTA stages its own 128 rows of A and its own half (BN/2 rows) of B, the leader issues
 // 256 x BN x 16 MMAs that read both CTAs' shared memory, each CTA keeps the accumulators of its 128
 // rows in its own TMEM and runs its own epilogue.  Halves the B traffic from L2 per CTA.
-template <int BN, bool A_MN, bool B_MN, int CG>
-__global__ void __launch_bounds__(kThreads, 1)
+// NGRP = number of 4-warp epilogue groups the CTA is launched with (2, or 4 for the ALU-bound GELU
+// epilogues, which then store straight from registers and leave all shared memory to the ring).
+template <int BN, bool A_MN, bool B_MN, int CG, int NGRP>
+__global__ void __launch_bounds__(64 + 160 * NGRP, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                    const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
                    const __grid_constant__ CUtensorMap tma_aux, int K, int num_m, int num_n, int splits,
-                   int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, EpiParams ep) {
+                   int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, EpiParams ep,
+                   long long* dbg) {
   constexpr int BNL = BN / CG;                       // B rows staged by this CTA
   constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BNL * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN;
@@ -212,10 +215,17 @@ __global__ void __launch_bounds__(kThreads, 1)
   uint64_t* empty = bars + kMaxStages;
   uint64_t* tfull = bars + 2 * kMaxStages;
   uint64_t* tempty = tfull + 2;
-  uint64_t* auxfull = tempty + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(auxfull + kMaxBuf);
+  uint64_t* auxfull = tempty + 2;                    // [group][buffer]: aux tile landed (and buffer free)
+  uint64_t* staged = auxfull + kMaxBuf;              // [group][buffer]: output data staged by the 128 threads
+  uint64_t* freeb = staged + kMaxBuf;                // [group][buffer]: TMA store drained the buffer
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(freeb + kMaxBuf);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Hardware warps: 0 .. 4*NGRP-1 epilogue (TMEM -> registers -> staging smem), 4*NGRP .. 5*NGRP-1 one
+  // store warp per epilogue group (issues the TMA stores / aux loads, recycles staging buffers), then
+  // the TMA producer and the MMA issuer.  Logical `warp`: 0 TMA, 1 MMA, 2.. epilogue, -1 store warp.
+  const int lane = threadIdx.x & 31;
+  const int hw_warp = threadIdx.x >> 5;
+  const int warp = hw_warp >= 5 * NGRP ? hw_warp - 5 * NGRP : (hw_warp >= 4 * NGRP ? -1 : hw_warp + 2);
   const int total_kb = (K + BK - 1) / BK;
   const int total_work = num_m * num_n * splits;
 
@@ -235,7 +245,11 @@ __global__ void __launch_bounds__(kThreads, 1)
       ptx::mbar_init(&tfull[s], 1);
       ptx::mbar_init(&tempty[s], 4 * ngroups * CG);   // epilogue warps of both CTAs release the leader
     }
-    for (int s = 0; s < kMaxBuf; ++s) ptx::mbar_init(&auxfull[s], 1);
+    for (int s = 0; s < kMaxBuf; ++s) {
+      ptx::mbar_init(&auxfull[s], 1);
+      ptx::mbar_init(&staged[s], 128);
+      ptx::mbar_init(&freeb[s], 1);
+    }
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
@@ -337,14 +351,14 @@ __global__ void __launch_bounds__(kThreads, 1)
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
-  } else {
+  } else if (warp >= 2) {
     // ================================ epilogue ==============================================
     // One or two groups of four warps; a group covers all 128 TMEM lanes (one lane quarter per
     // warp) and takes every ngroups-th column chunk of a tile.
     const int grp = (warp - 2) >> 2;
-    const int q = warp & 3;                 // TMEM lane quarter this warp may touch
+    const int q = hw_warp & 3;              // TMEM lane quarter this (hardware) warp may touch
     const int row = q * 32 + lane;          // row of the tile owned by this thread
-    const int et = (threadIdx.x - 64) & 127;  // 0..127 within the group
+    const int et = threadIdx.x & 127;         // 0..127 within the group (epilogue warps are hardware warps 0..)
     const float alpha = ep.alpha ? *ep.alpha : 1.f;
     int as = 0;
     uint32_t aphase = 0;
@@ -369,71 +383,75 @@ __global__ void __launch_bounds__(kThreads, 1)
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     } else {
-      // ---- staged epilogue: TMEM -> registers -> swizzled smem -> TMA store / reduce-add ----
+      // ---- staged epilogue: TMEM -> registers -> swizzled smem; the group's store warp ships it ----
       const bool c32 = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_ACCUM || !ep.c_bf16);
       const int CW = c32 ? 32 : 64;         // columns per 128-byte staging row
       const int CH = BN / CW;               // chunks per tile
-      const int CHG = CH / ngroups;         // chunks per tile handled by this group
       const bool aux_tma = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU) && !aux_direct;
-      const bool reduce = (ep.kind == NSB_EPI_ACCUM) && (ep.accumulate || splits > 1);
       const bool has_bias = ep.bias != nullptr && ep.kind != NSB_EPI_ACCUM && ep.kind != NSB_EPI_DGELU;
-      const int my_tiles = (total_work - unit + nunits - 1) / nunits;
-      const int total_chunks = my_tiles * CHG;
+      const bool scaled = alpha != 1.f;
       uint8_t* pool = smem_stg + grp * nbuf * STG_BYTES;
       uint64_t* auxbar = auxfull + grp * nbuf;
-      const int bar_id = 1 + grp;
+      uint64_t* stgbar = staged + grp * nbuf;
+      uint64_t* freebar = freeb + grp * nbuf;
+      const bool rec = dbg != nullptr && blockIdx.x == 0 && hw_warp == 0 && lane == 0;
+      int nrec = 0;
+      auto stamp = [&]() { if (rec && nrec < 1000) dbg[nrec++] = clock64(); };
       int emit = 0;                         // staging-buffer uses so far (buffer = emit % nbuf)
-      int next_aux = 0;                     // next (group-local) chunk whose aux tile was not requested yet
-      auto prefetch_aux = [&](int upto) {   // elected thread only
-        while (next_aux <= upto && next_aux < total_chunks) {
-          const int j = next_aux++;
-          const TileCoord t = tile_of(unit + (j / CHG) * nunits, num_m, num_n);
-          const int b = j % nbuf;
-          ptx::mbar_expect_tx(&auxbar[b], STG_BYTES);
-          ptx::tma_load_2d(pool + b * STG_BYTES, &tma_aux, &auxbar[b],
-                           t.n_blk * BN + ((j % CHG) * ngroups + grp) * CW, (t.m_blk * CG + static_cast<int>(rank)) * BM);
-        }
+      // acquire the staging buffer of the next emission: with an aux tile the TMA load that fills it
+      // is also the "buffer is free" signal
+      auto acquire = [&]() -> uint8_t* {
+        const int b = emit % nbuf, u = emit / nbuf;
+        if (aux_tma) ptx::mbar_wait(&auxbar[b], u & 1);
+        else ptx::mbar_wait(&freebar[b], (u & 1) ^ 1);
+        return pool + b * STG_BYTES;
       };
-      // make the staged data visible to the async proxy, wait until the buffer about to be
-      // reused is drained, then one thread issues the store
-      auto emit_store = [&](const CUtensorMap* map, int col, int rowg, bool red) {
+      auto publish = [&]() {                // data staged -> store warp
         ptx::fence_proxy_async();
-        if (et == 0) ptx::bulk_wait_read<0>();
-        ptx::named_bar_sync(bar_id, 128);
-        if (et == 0) {
-          const uint8_t* src = pool + (emit % nbuf) * STG_BYTES;
-          if (red) ptx::tma_reduce_add_2d(map, src, col, rowg);
-          else ptx::tma_store_2d(map, src, col, rowg);
-          ptx::bulk_commit();
-        }
+        ptx::mbar_arrive(&stgbar[emit % nbuf]);
         ++emit;
       };
-      if (aux_tma && et == 0) prefetch_aux(nbuf - 1);
-      int g = 0;                            // group-local chunk counter (aux kinds: emit == g)
       for (int w = unit; w < total_work; w += nunits) {
         const TileCoord t = tile_of(w, num_m, num_n);
         ptx::mbar_wait(&tfull[as], aphase);
         ptx::tc_fence_after();
         const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
 #pragma unroll 1
-        for (int c = grp; c < CH; c += ngroups, ++g) {
+        for (int c = grp; c < CH; c += ngroups) {
           const int n0 = t.n_blk * BN + c * CW;
           const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN + c * CW);
-          uint8_t* buf = pool + (emit % nbuf) * STG_BYTES;
+          stamp();                                  // [0] chunk start
           if (c32) {
             float v[32];
-            ptx::tmem_ld_32x32(taddr, v);
+            ptx::tmem_ld_32x32_async(taddr, v);
+            uint8_t* buf = acquire();
+            ptx::tmem_wait_ld32(v);
+            stamp();                                // [1] accumulators + buffer ready
+            if (scaled) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= alpha;
+              for (int j = 0; j < 32; ++j) v[j] *= alpha;
+            }
             if (has_bias) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] += (n0 + j < ep.N) ? __ldg(ep.bias + n0 + j) : 0.f;
             }
             if (ep.kind == NSB_EPI_RESIDUAL) {
-              ptx::mbar_wait(&auxbar[g % nbuf], (g / nbuf) & 1);
+              const bool ok = (m0 + row < ep.M) && (n0 + 32 <= ep.N);
+              const float4* rp = reinterpret_cast<const float4*>(
+                  static_cast<const float*>(ep.aux) + static_cast<size_t>(ok ? m0 + row : 0) * ep.ldc + (ok ? n0 : 0));
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                const float4 a = *reinterpret_cast<const float4*>(buf + stg_off(row, j));
+                float4 a;
+                if (aux_tma) a = *reinterpret_cast<const float4*>(buf + stg_off(row, j));
+                else if (ok) a = __ldg(rp + j);
+                else {
+                  const float* rs = static_cast<const float*>(ep.aux) + static_cast<size_t>(m0 + row) * ep.ldc;
+                  const bool rok = m0 + row < ep.M;
+                  a.x = (rok && n0 + 4 * j + 0 < ep.N) ? rs[n0 + 4 * j + 0] : 0.f;
+                  a.y = (rok && n0 + 4 * j + 1 < ep.N) ? rs[n0 + 4 * j + 1] : 0.f;
+                  a.z = (rok && n0 + 4 * j + 2 < ep.N) ? rs[n0 + 4 * j + 2] : 0.f;
+                  a.w = (rok && n0 + 4 * j + 3 < ep.N) ? rs[n0 + 4 * j + 3] : 0.f;
+                }
                 if (ep.c_bf16) {
                   v[4 * j] = a.x + round_bf16(v[4 * j]); v[4 * j + 1] = a.y + round_bf16(v[4 * j + 1]);
                   v[4 * j + 2] = a.z + round_bf16(v[4 * j + 2]); v[4 * j + 3] = a.w + round_bf16(v[4 * j + 3]);
@@ -445,91 +463,167 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
             for (int j = 0; j < 8; ++j)
               *reinterpret_cast<float4*>(buf + stg_off(row, j)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-            emit_store(&tma_c, n0, m0, reduce);
+            stamp();                                // [2] staged
+            publish();
+            stamp();                                // [3] published
             if (ep.kind == NSB_EPI_GELU) {  // fp32 C2 (not used by the bf16 model path, kept complete)
-              buf = pool + (emit % nbuf) * STG_BYTES;
+              buf = acquire();
 #pragma unroll
               for (int j = 0; j < 8; ++j)
                 *reinterpret_cast<float4*>(buf + stg_off(row, j)) =
                     make_float4(gelu_exact(v[4 * j]), gelu_exact(v[4 * j + 1]), gelu_exact(v[4 * j + 2]), gelu_exact(v[4 * j + 3]));
-              emit_store(&tma_c2, n0, m0, false);
+              publish();
             }
           } else {
-            // bf16 output: 64 columns per staging row, processed as two 32-column halves.
-            // GELU: a second pass re-reads the accumulators from TMEM for the activated output.
-            const int npass = (ep.kind == NSB_EPI_GELU) ? 2 : 1;
-            for (int pass = 0; pass < npass; ++pass) {
-              if (pass == 1) buf = pool + (emit % nbuf) * STG_BYTES;
-              if (ep.kind == NSB_EPI_DGELU && aux_tma) ptx::mbar_wait(&auxbar[g % nbuf], (g / nbuf) & 1);
-#pragma unroll 1
-              for (int half = 0; half < 2; ++half) {
-                const int nh = n0 + half * 32;
-                uint4 hraw[4];
-                if (ep.kind == NSB_EPI_DGELU) {
-                  if (aux_tma) {
+            // bf16 output: 64 columns per staging row = two 32-column TMEM loads (issued back to back).
+            // GELU: the activated output is a second emission computed from the same registers.
+            float va[32], vb[32];
+            ptx::tmem_ld_32x32_async(taddr, va);
+            ptx::tmem_ld_32x32_async(taddr + 32, vb);
+            uint4 hraw[8];
+            if (ep.kind == NSB_EPI_DGELU && !aux_tma) {
+              // pre-activation read straight from global: 128 contiguous bytes of this thread's row
+              const bool ok = (m0 + row < ep.M) && (n0 + 64 <= ep.N);
+              const uint4* hp = reinterpret_cast<const uint4*>(
+                  static_cast<const __nv_bfloat16*>(ep.aux) + static_cast<size_t>(ok ? m0 + row : 0) * ep.ldc + (ok ? n0 : 0));
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) hraw[j] = *reinterpret_cast<const uint4*>(buf + stg_off(row, half * 4 + j));
-                  } else {
-                    // pre-activation read straight from global: 64 contiguous bytes of this thread's row
-                    const bool ok = (m0 + row < ep.M) && (nh + 32 <= ep.N);
-                    const uint4* hp = reinterpret_cast<const uint4*>(
-                        static_cast<const __nv_bfloat16*>(ep.aux) + static_cast<size_t>(ok ? m0 + row : 0) * ep.ldc + (ok ? nh : 0));
+              for (int j = 0; j < 8; ++j) hraw[j] = ok ? __ldg(hp + j) : make_uint4(0, 0, 0, 0);
+              if (!ok && (m0 + row < ep.M)) {  // ragged right edge: element-wise
+                __nv_bfloat16 tmp[64];
+                for (int j = 0; j < 64; ++j)
+                  tmp[j] = (n0 + j < ep.N) ? static_cast<const __nv_bfloat16*>(ep.aux)[static_cast<size_t>(m0 + row) * ep.ldc + n0 + j]
+                                           : __float2bfloat16_rn(0.f);
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) hraw[j] = ok ? __ldg(hp + j) : make_uint4(0, 0, 0, 0);
-                    if (!ok && (m0 + row < ep.M)) {  // ragged right edge: element-wise
-                      __nv_bfloat16 tmp[32];
-                      for (int j = 0; j < 32; ++j)
-                        tmp[j] = (nh + j < ep.N) ? static_cast<const __nv_bfloat16*>(ep.aux)[static_cast<size_t>(m0 + row) * ep.ldc + nh + j]
-                                                 : __float2bfloat16_rn(0.f);
+                for (int j = 0; j < 8; ++j) hraw[j] = reinterpret_cast<const uint4*>(tmp)[j];
+              }
+            }
+            uint8_t* buf = acquire();
+            if (ep.kind == NSB_EPI_DGELU && aux_tma) {
 #pragma unroll
-                      for (int j = 0; j < 4; ++j) hraw[j] = reinterpret_cast<const uint4*>(tmp)[j];
-                    }
-                  }
-                }
-                float v[32];
-                ptx::tmem_ld_32x32(taddr + half * 32, v);
+              for (int j = 0; j < 8; ++j) hraw[j] = *reinterpret_cast<const uint4*>(buf + stg_off(row, j));
+            }
+            ptx::tmem_wait_ld32(va);
+            ptx::tmem_wait_ld32(vb);
+            stamp();                                // [1] accumulators + buffer ready
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              float* v = half ? vb : va;
+              const int nh = n0 + half * 32;
+              if (scaled) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] *= alpha;
-                if (has_bias) {
-#pragma unroll
-                  for (int j = 0; j < 32; ++j) v[j] += (nh + j < ep.N) ? __ldg(ep.bias + nh + j) : 0.f;
-                }
-                if (ep.kind == NSB_EPI_DGELU) {
-#pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-                    const float2 h0 = unpack_bf16x2(hraw[j].x), h1 = unpack_bf16x2(hraw[j].y),
-                                 h2 = unpack_bf16x2(hraw[j].z), h3 = unpack_bf16x2(hraw[j].w);
-                    v[8 * j] = round_bf16(v[8 * j]) * gelu_fast_grad(h0.x);
-                    v[8 * j + 1] = round_bf16(v[8 * j + 1]) * gelu_fast_grad(h0.y);
-                    v[8 * j + 2] = round_bf16(v[8 * j + 2]) * gelu_fast_grad(h1.x);
-                    v[8 * j + 3] = round_bf16(v[8 * j + 3]) * gelu_fast_grad(h1.y);
-                    v[8 * j + 4] = round_bf16(v[8 * j + 4]) * gelu_fast_grad(h2.x);
-                    v[8 * j + 5] = round_bf16(v[8 * j + 5]) * gelu_fast_grad(h2.y);
-                    v[8 * j + 6] = round_bf16(v[8 * j + 6]) * gelu_fast_grad(h3.x);
-                    v[8 * j + 7] = round_bf16(v[8 * j + 7]) * gelu_fast_grad(h3.y);
-                  }
-                } else if (pass == 1) {
-#pragma unroll
-                  for (int j = 0; j < 32; ++j) v[j] = gelu_fast(round_bf16(v[j]));
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                  *reinterpret_cast<uint4*>(buf + stg_off(row, half * 4 + j)) =
-                      make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                                 pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
               }
-              emit_store(pass == 0 ? &tma_c : &tma_c2, n0, m0, false);
+              if (has_bias) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] += (nh + j < ep.N) ? __ldg(ep.bias + nh + j) : 0.f;
+              }
+              if (ep.kind == NSB_EPI_DGELU) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const uint4 hr = hraw[half * 4 + j];
+                  const float2 h0 = unpack_bf16x2(hr.x), h1 = unpack_bf16x2(hr.y), h2 = unpack_bf16x2(hr.z), h3 = unpack_bf16x2(hr.w);
+                  v[8 * j] = round_bf16(v[8 * j]) * gelu_fast_grad(h0.x);
+                  v[8 * j + 1] = round_bf16(v[8 * j + 1]) * gelu_fast_grad(h0.y);
+                  v[8 * j + 2] = round_bf16(v[8 * j + 2]) * gelu_fast_grad(h1.x);
+                  v[8 * j + 3] = round_bf16(v[8 * j + 3]) * gelu_fast_grad(h1.y);
+                  v[8 * j + 4] = round_bf16(v[8 * j + 4]) * gelu_fast_grad(h2.x);
+                  v[8 * j + 5] = round_bf16(v[8 * j + 5]) * gelu_fast_grad(h2.y);
+                  v[8 * j + 6] = round_bf16(v[8 * j + 6]) * gelu_fast_grad(h3.x);
+                  v[8 * j + 7] = round_bf16(v[8 * j + 7]) * gelu_fast_grad(h3.y);
+                }
+              }
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                *reinterpret_cast<uint4*>(buf + stg_off(row, half * 4 + j)) =
+                    make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                               pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+            }
+            stamp();                                // [2] staged
+            publish();
+            stamp();                                // [3] published
+            if (ep.kind == NSB_EPI_GELU) {
+              buf = acquire();
+#pragma unroll
+              for (int half = 0; half < 2; ++half) {
+                float* v = half ? vb : va;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  float y[8];
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) y[i] = gelu_fast(round_bf16(v[8 * j + i]));
+                  *reinterpret_cast<uint4*>(buf + stg_off(row, half * 4 + j)) =
+                      make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
+                }
+              }
+              publish();
             }
           }
-          // stores up to chunk g-1 have drained (emit_store waited): their buffers may be refilled
-          if (aux_tma && et == 0) prefetch_aux(g + nbuf - 1);
         }
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
-      if (et == 0) ptx::bulk_wait_all();
+    }
+  }
+  if (warp == -1 && tma_epi) {
+    // ================================ store warp (one per epilogue group) ====================
+    // Walks the same emission sequence as its group: waits until the 128 threads have staged a
+    // buffer, issues the TMA store / reduce-add, keeps nbuf-2 stores in flight, and recycles a
+    // buffer (release it, or refill it with the aux tile 2 chunks ahead) once its store has drained.
+    const int grp = hw_warp - 4 * NGRP;
+    if (grp < ngroups) {
+      const bool c32 = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_ACCUM || !ep.c_bf16);
+      const int CW = c32 ? 32 : 64;
+      const int CH = BN / CW, CHG = CH / ngroups;
+      const int EPC = (ep.kind == NSB_EPI_GELU) ? 2 : 1;    // emissions per chunk
+      const bool aux_tma = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU) && !aux_direct;
+      const bool reduce = (ep.kind == NSB_EPI_ACCUM) && (ep.accumulate || splits > 1);
+      const int my_tiles = (total_work - unit + nunits - 1) / nunits;
+      const int total_chunks = my_tiles * CHG;
+      const int total_emit = total_chunks * EPC;
+      uint8_t* pool = smem_stg + grp * nbuf * STG_BYTES;
+      uint64_t* auxbar = auxfull + grp * nbuf;
+      uint64_t* stgbar = staged + grp * nbuf;
+      uint64_t* freebar = freeb + grp * nbuf;
+      auto coords = [&](int chunk, int& col, int& rowg) {
+        const TileCoord t = tile_of(unit + (chunk / CHG) * nunits, num_m, num_n);
+        col = t.n_blk * BN + ((chunk % CHG) * ngroups + grp) * CW;
+        rowg = (t.m_blk * CG + static_cast<int>(rank)) * BM;
+      };
+      auto load_aux = [&](int chunk) {       // elected lane only
+        int col, rowg;
+        coords(chunk, col, rowg);
+        const int b = chunk % nbuf;
+        ptx::mbar_expect_tx(&auxbar[b], STG_BYTES);
+        ptx::tma_load_2d(pool + b * STG_BYTES, &tma_aux, &auxbar[b], col, rowg);
+      };
+      if (aux_tma && ptx::elect_one()) {
+        for (int j = 0; j < nbuf && j < total_chunks; ++j) load_aux(j);
+      }
+      __syncwarp();
+      const int inflight = nbuf - 2;         // stores allowed to be still reading their buffer
+      for (int e = 0; e < total_emit; ++e) {
+        const int b = e % nbuf;
+        ptx::mbar_wait(&stgbar[b], (e / nbuf) & 1);
+        if (ptx::elect_one()) {
+          int col, rowg;
+          coords(e / EPC, col, rowg);
+          const CUtensorMap* map = (EPC == 2 && (e & 1)) ? &tma_c2 : &tma_c;
+          if (reduce) ptx::tma_reduce_add_2d(map, pool + b * STG_BYTES, col, rowg);
+          else ptx::tma_store_2d(map, pool + b * STG_BYTES, col, rowg);
+          ptx::bulk_commit();
+          if (e >= inflight) {
+            if (inflight == 1) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<2>();
+            const int done = e - inflight;    // this emission's buffer has been read out
+            if (aux_tma) { if (done + nbuf < total_chunks) load_aux(done + nbuf); }
+            else ptx::mbar_arrive(&freebar[done % nbuf]);
+          }
+        }
+        __syncwarp();
+      }
+      if (ptx::elect_one()) ptx::bulk_wait_all();
+      __syncwarp();
     }
   }
 
@@ -610,14 +704,15 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint
   return 0;
 }
 
+static long long* g_gemm_dbg = nullptr;
 struct LaunchPlan {
   CUtensorMap ta, tb, tc, tc2, taux;
   int K, num_m, num_n, splits, kb_per_split, stages, nbuf, tma_epi, ngroups, aux_direct;
 };
 
-template <int BN, bool A_MN, bool B_MN, int CG>
+template <int BN, bool A_MN, bool B_MN, int CG, int NGRP = 2>
 static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_t stream) {
-  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, CG>;
+  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, CG, NGRP>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemLimit));
@@ -630,7 +725,7 @@ static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_
   const int grid = (total < units ? total : units) * CG;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3(64 + 160 * NGRP);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -641,7 +736,7 @@ static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
-                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, ep);
+                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, ep, g_gemm_dbg);
   NSB_REQUIRE(e == cudaSuccess, "gemm_tc: launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("gemm_tc");
@@ -716,9 +811,15 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   // ALU-heavy bf16 GELU epilogues get a second epilogue group; GELU backward then reads its
   // pre-activation tile straight from global (no aux staging buffers)
   const bool heavy = tma_epi && ep.c_bf16 && (ep.kind == NSB_EPI_GELU || ep.kind == NSB_EPI_DGELU);
-  lp.ngroups = (heavy && force_groups != 1) || (tma_epi && force_groups == 2 && ep.kind != NSB_EPI_RESIDUAL) ? 2 : 1;
+  // Epilogue groups: the ALU-heavy GELU epilogues get two groups (8 warps); plain stores, accumulation
+  // and the residual add (whose fp32 aux tile arrives by TMA into the staging buffers) run on one group,
+  // which leaves more shared memory to the operand ring.
+  lp.ngroups = ((heavy && force_groups != 1) || (tma_epi && force_groups == 2)) ? 2 : 1;
+  if (ep.kind == NSB_EPI_RESIDUAL) lp.ngroups = 1;
+  // GELU backward with two groups reads its pre-activation tile straight from global (no room for
+  // aux staging buffers next to the output buffers of two groups)
   lp.aux_direct = (ep.kind == NSB_EPI_DGELU && lp.ngroups == 2) ? 1 : 0;
-  lp.nbuf = tma_epi ? ((has_aux && !lp.aux_direct) ? 4 : 2) : 0;
+  lp.nbuf = tma_epi ? ((has_aux && !lp.aux_direct) ? 4 : (lp.ngroups == 2 ? 3 : 4)) : 0;
   int stages = kMaxStages;
   while (stages > 2 && smem_bytes_for(bn / cg, stages, lp.nbuf * lp.ngroups) > kSmemLimit) --stages;
   lp.stages = stages;
@@ -762,9 +863,12 @@ void nsb_gemm_debug_config(int force_bn, int force_splits, int force_simt) {
   g_force_splits = force_splits;
   g_force_simt = force_simt == 1;
   g_force_direct_epi = force_simt == 2;
-  g_force_groups = force_simt == 3 ? 1 : (force_simt == 4 ? 2 : 0);  // 3: one epilogue group, 4: two
+  g_force_groups = force_simt == 3 ? 1 : (force_simt == 4 ? 2 : (force_simt == 7 ? 4 : 0));  // 3: one epilogue group, 4: two, 7: four (register stores)
   g_force_cg = force_simt == 5 ? 1 : (force_simt == 6 ? 2 : 0);      // 5: single-CTA tiles, 6: CTA pairs
 }
+
+// device buffer (>= 1024 int64) receiving clock64 stamps of CTA 0's first epilogue thread; NULL = off
+void nsb_gemm_debug_timing(void* device_buffer) { nsb::g_gemm_dbg = static_cast<long long*>(device_buffer); }
 
 int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
   NSB_REQUIRE(a != nullptr, "gemm: null args");

@@ -181,6 +181,9 @@ class GPT(nn.Module):
         self._arena: ParamArena | None = None
         self._acts = {}
         self._grad_sync = None          # set by nanosandbox_b200.ddp.DistributedDataParallel
+        # bf16 path: GELU as its own memory-bound kernels (faster on B200 than the fused GEMM epilogues,
+        # whose eight epilogue warps cannot hide the erf math behind a K = 768 mainloop)
+        self.split_gelu = True
         self._micro_step_has_grads = False
 
     # ------------------------------------------------------------------ nanoGPT surface
@@ -356,8 +359,13 @@ class GPT(nn.Module):
             ops.gemm(M, C, C, a.att[l], C, True, W(pre + "attn.c_proj.weight"), C, True, a.xmid[l], C,
                      EPI_RESIDUAL, aux=a.x[l], bias=bias(pre + "attn.c_proj.bias"), stream=st)
             ops.layernorm_fwd(a.xmid[l], P(pre + "ln_2.weight"), bias(pre + "ln_2.bias"), a.ln2[l], s[2], s[3], 1e-5, st)
-            ops.gemm(M, 4 * C, C, a.ln2[l], C, True, W(pre + "mlp.c_fc.weight"), C, True, a.fch[l], 4 * C,
-                     EPI_GELU, C2=a.fca[l], bias=bias(pre + "mlp.c_fc.bias"), stream=st)
+            if lowp and self.split_gelu:
+                ops.gemm(M, 4 * C, C, a.ln2[l], C, True, W(pre + "mlp.c_fc.weight"), C, True, a.fch[l], 4 * C,
+                         EPI_STORE, bias=bias(pre + "mlp.c_fc.bias"), stream=st)
+                ops.gelu_fwd(a.fch[l], a.fca[l], st)
+            else:
+                ops.gemm(M, 4 * C, C, a.ln2[l], C, True, W(pre + "mlp.c_fc.weight"), C, True, a.fch[l], 4 * C,
+                         EPI_GELU, C2=a.fca[l], bias=bias(pre + "mlp.c_fc.bias"), stream=st)
             ops.gemm(M, C, 4 * C, a.fca[l], 4 * C, True, W(pre + "mlp.c_proj.weight"), 4 * C, True, a.x[l + 1], C,
                      EPI_RESIDUAL, aux=a.xmid[l], bias=bias(pre + "mlp.c_proj.bias"), stream=st)
         ops.layernorm_fwd(a.x[L], P("transformer.ln_f.weight"), bias("transformer.ln_f.bias"), a.lnf,
@@ -416,8 +424,13 @@ class GPT(nn.Module):
             dres, dres_a = a.dres[cur], act(a.dres[cur], a.dres_lowp)
             # MLP
             wgrad(dres_a, C, a.fca[l], 4 * C, pre + "mlp.c_proj", C, 4 * C)
-            ops.gemm(M, 4 * C, C, dres_a, C, True, W(pre + "mlp.c_proj.weight"), 4 * C, False, a.dh, 4 * C,
-                     EPI_DGELU, aux=a.fch[l], stream=st)
+            if lowp and self.split_gelu:
+                ops.gemm(M, 4 * C, C, dres_a, C, True, W(pre + "mlp.c_proj.weight"), 4 * C, False, a.dh, 4 * C,
+                         EPI_STORE, stream=st)
+                ops.gelu_bwd(a.dh, a.fch[l], st)
+            else:
+                ops.gemm(M, 4 * C, C, dres_a, C, True, W(pre + "mlp.c_proj.weight"), 4 * C, False, a.dh, 4 * C,
+                         EPI_DGELU, aux=a.fch[l], stream=st)
             wgrad(a.dh, 4 * C, a.ln2[l], C, pre + "mlp.c_fc", 4 * C, C)
             ops.gemm(M, C, 4 * C, a.dh, 4 * C, True, W(pre + "mlp.c_fc.weight"), C, False, a.dln, C, EPI_STORE, stream=st)
             ops.layernorm_bwd(a.dln, a.xmid[l], P(pre + "ln_2.weight"), s[2], s[3], dres, a.dres[cur ^ 1],

@@ -120,6 +120,15 @@ def scale_f32(x, scale, stream=None):
           "scale_f32")
 
 
+def gelu_fwd(h, a, stream=None):
+    check(_lib.load().nsb_gelu_fwd_bf16(h.data_ptr(), a.data_ptr(), h.numel(), stream or stream_handle()), "gelu_fwd")
+
+
+def gelu_bwd(da, h, stream=None):
+    """in place: da <- da * gelu'(h)"""
+    check(_lib.load().nsb_gelu_bwd_bf16(da.data_ptr(), h.data_ptr(), h.numel(), stream or stream_handle()), "gelu_bwd")
+
+
 def colsum(dy, db, accumulate, stream=None):
     M, N = dy.shape
     check(_lib.load().nsb_colsum(dy.data_ptr(), dtype_code(dy), dy.stride(0), db.data_ptr(), int(accumulate),

@@ -154,6 +154,19 @@ def test_grad_norm_and_adamw_match_torch():
         assert_close(lowp, ref, 4e-3, "bf16 shadow")
 
 
+def test_gelu_standalone_bf16():
+    torch.manual_seed(9)
+    h = (torch.randn(1000, 3072, device=DEV) * 2).to(torch.bfloat16)
+    a = torch.empty_like(h)
+    ops.gelu_fwd(h, a)
+    assert_close(a, F.gelu(h.float()), 4e-3, "gelu fwd")
+    hx = h.float().clone().requires_grad_(True)
+    da = torch.randn_like(h)
+    F.gelu(hx).backward(da.float())
+    ops.gelu_bwd(da, h)
+    assert_close(da, hx.grad, 4e-3, "gelu bwd")
+
+
 def test_casts_and_colsum():
     torch.manual_seed(4)
     x = torch.randn(100003, device=DEV)

@@ -105,6 +105,13 @@ def main():
     t = timeit(lambda: ops.cross_entropy_bwd(logits, tg, ls, st, None, V))
     by = Mt * V * 4
     print(f"cross-ent bwd  {t*1e3:8.1f} us {by/t/1e6:7.1f} GB/s ({by/t/1e6/PEAKS['hbm_gbs']*100:5.1f}% of measured)")
+    hh = torch.randn(Mt, 4 * Cc, device=DEV).to(torch.bfloat16); aa = torch.empty_like(hh)
+    t = timeit(lambda: ops.gelu_fwd(hh, aa))
+    by = Mt * 4 * Cc * 4
+    print(f"gelu fwd       {t*1e3:8.1f} us {by/t/1e6:7.1f} GB/s ({by/t/1e6/PEAKS['hbm_gbs']*100:5.1f}% of measured)")
+    t = timeit(lambda: ops.gelu_bwd(aa, hh))
+    by = Mt * 4 * Cc * 6
+    print(f"gelu bwd       {t*1e3:8.1f} us {by/t/1e6:7.1f} GB/s ({by/t/1e6/PEAKS['hbm_gbs']*100:5.1f}% of measured)")
     n = 124_400_640 // 1024 * 1024
     p = torch.randn(n, device=DEV); g = torch.randn(n, device=DEV); m = torch.zeros(n, device=DEV); v = torch.zeros(n, device=DEV)
     lp = torch.empty(n, device=DEV, dtype=torch.bfloat16)

@@ -26,15 +26,15 @@ def run(name, M, N, K, a_k, b_k, epi, accumulate=False, cfgs=()):
 
 Mt, Cc = 12288, 768
 E = _lib
-base = [("default", (0, 0, 0)), ("bn256 1grp", (256, 0, 3)), ("bn256 2grp", (256, 0, 4)), ("bn128 1grp", (128, 0, 3)), ("bn128 2grp", (128, 0, 4))]
+base = [("default", (0, 0, 0)), ("1grp tma", (0, 0, 3)), ("2grp tma", (0, 0, 4)), ("4grp regstore", (0, 0, 7)), ("single-cta", (0, 0, 5))]
 run("fc fwd gelu", Mt, 4 * Cc, Cc, True, True, E.EPI_GELU, cfgs=base)
 run("fc fwd store-only", Mt, 4 * Cc, Cc, True, True, E.EPI_STORE, cfgs=base)
 run("proj dgrad dgelu", Mt, 4 * Cc, Cc, True, False, E.EPI_DGELU, cfgs=base)
-run("attn proj res", Mt, Cc, Cc, True, True, E.EPI_RESIDUAL, cfgs=base[:2] + base[3:4])
-run("mlp proj res", Mt, Cc, 4 * Cc, True, True, E.EPI_RESIDUAL, cfgs=base[:2] + base[3:4])
-run("qkv fwd", Mt, 3 * Cc, Cc, True, True, E.EPI_STORE, cfgs=base[:2] + base[3:4])
-sp = [("default", (0, 0, 0))] + [(f"splits {s}", (0, s, 0)) for s in (1, 2, 3, 4, 5, 6, 8, 12, 16)]
+run("attn proj res", Mt, Cc, Cc, True, True, E.EPI_RESIDUAL, cfgs=[base[0], base[4]])
+run("mlp proj res", Mt, Cc, 4 * Cc, True, True, E.EPI_RESIDUAL, cfgs=[base[0], base[4]])
+run("qkv fwd", Mt, 3 * Cc, Cc, True, True, E.EPI_STORE, cfgs=[base[0], base[2], base[4]])
+sp = [("default", (0, 0, 0)), ("single-cta", (0, 0, 5))]
 run("qkv wgrad", 3 * Cc, Cc, Mt, False, False, E.EPI_ACCUM, True, cfgs=sp)
-run("attn proj wgrad", Cc, Cc, Mt, False, False, E.EPI_ACCUM, True, cfgs=sp + [("bn128 s8", (128, 8, 0)), ("bn128 s4", (128, 4, 0))])
+run("attn proj wgrad", Cc, Cc, Mt, False, False, E.EPI_ACCUM, True, cfgs=sp)
 run("fc wgrad", 4 * Cc, Cc, Mt, False, False, E.EPI_ACCUM, True, cfgs=sp)
 run("mlp proj wgrad", Cc, 4 * Cc, Mt, False, False, E.EPI_ACCUM, True, cfgs=sp)
