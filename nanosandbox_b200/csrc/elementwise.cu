@@ -148,11 +148,12 @@ __global__ void __launch_bounds__(256)
 }
 
 // Stage 1 of the backward: dx (+ residual gradient) per row, per-CTA column partials of dw/db.
-// part layout: [gridDim.x][2][C].  Register diet (3 CTAs of 8 warps per SM): only dy and x of the
-// row stay live between the two passes, xhat and dy*w are recomputed (w comes from L1), and the
-// db accumulators exist only when a bias gradient is wanted.
+// part layout: [gridDim.x][2][C].  All three row inputs (dy, x, incoming residual gradient) are
+// loaded before anything is reduced, so a row costs one memory latency; xhat and dy*w are
+// recomputed in the second pass (w comes from L1) and the db accumulators exist only when a bias
+// gradient is wanted, which keeps two CTAs of 8 warps resident per SM.
 template <int NV, typename DyT, bool HAS_DB>
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, 2)
     layernorm_bwd_kernel(const DyT* __restrict__ dy, const float* __restrict__ x,
                          const float* __restrict__ w, const float* __restrict__ mean,
                          const float* __restrict__ rstd, const float* __restrict__ dres_in,
@@ -170,7 +171,7 @@ __global__ void __launch_bounds__(256, 3)
   for (int row = blockIdx.x * 8 + warp; row < M; row += gridDim.x * 8) {
     const size_t off = static_cast<size_t>(row) * C;
     const float mu = mean[row], rs = rstd[row];
-    float4 dyv[NV], xv[NV];
+    float4 dyv[NV], xv[NV], rv[NV];   // every global read of the row is issued up front: one memory latency per row
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
@@ -178,6 +179,7 @@ __global__ void __launch_bounds__(256, 3)
       if (c < C) {
         dyv[j] = Vec4IO<DyT>::load(dy + off + c);
         xv[j] = Vec4IO<float>::load(x + off + c);
+        rv[j] = dres_in != nullptr ? Vec4IO<float>::load(dres_in + off + c) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
 #pragma unroll
@@ -205,10 +207,7 @@ __global__ void __launch_bounds__(256, 3)
         const float4 xh = make_float4((xv[j].x - mu) * rs, (xv[j].y - mu) * rs, (xv[j].z - mu) * rs, (xv[j].w - mu) * rs);
         float4 o = make_float4(rs * (d.x * wv.x - c1 - xh.x * c2), rs * (d.y * wv.y - c1 - xh.y * c2),
                                rs * (d.z * wv.z - c1 - xh.z * c2), rs * (d.w * wv.w - c1 - xh.w * c2));
-        if (dres_in != nullptr) {
-          const float4 r = Vec4IO<float>::load(dres_in + off + c);
-          o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
-        }
+        o.x += rv[j].x; o.y += rv[j].y; o.z += rv[j].z; o.w += rv[j].w;
         Vec4IO<float>::store(dx + off + c, o);
         if (dx_lowp != nullptr) Vec4IO<__nv_bfloat16>::store(dx_lowp + off + c, o);
       }
@@ -690,7 +689,7 @@ int nsb_layernorm_fwd(const float* x, const float* w, const float* b, void* y, i
 
 static inline int ln_bwd_grid(int M) {
   int g = (M + 7) / 8;
-  const int cap = 3 * sm_count();  // 3 resident CTAs per SM; scratch contract: at most 4 x 160 slabs
+  const int cap = 2 * sm_count();  // 2 resident CTAs per SM; scratch contract: at most 4 x 160 slabs
   return g < cap ? (g < 1 ? 1 : g) : cap;
 }
 size_t nsb_layernorm_bwd_scratch_bytes(int M, int C) {
