@@ -344,7 +344,8 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
 // dV and dK accumulate in TMEM over the whole loop; dQ of the block goes TMEM -> swizzled smem ->
 // TMA reduce-add into an fp32 accumulator [B*T, C] shared by all key blocks (converted to bf16,
 // and re-zeroed, by attn_dq_convert_kernel).  Warps: 0 = TMA, 1 = MMA issue, 2..9 = two compute
-// groups, each taking 64 of the 128 query columns of every row.
+// groups, each taking 64 of the 128 query columns of every row, 10..13 = dQ write-back (so the
+// compute warps go straight from one block's probabilities to the next).
 // =============================================================================================
 namespace fabw {
 constexpr int BQ = 128, BKV = 128, HD = 64;
@@ -358,11 +359,49 @@ constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
 }  // namespace fabw
 
-__global__ void __launch_bounds__(320, 1)
+// 64 query columns of one key row: P^T = exp2(S^T*scale - lse[q]) and dS^T = P^T (dP^T - delta[q]),
+// returned as packed bf16 pairs.  MASK: causal mask on the diagonal block / padding columns.
+template <bool MASK>
+__device__ __forceinline__ void bwd_probs(uint32_t taddr, const float* lse2, const float* dlt, float scale_log2,
+                                          int col0, int row, int qlim, bool diag, uint32_t* pk, uint32_t* dk) {
+  using fatc::ex2;
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    float sv[32], dv[32];
+    ptx::tmem_ld_32x32_async(taddr + fabw::C_S + c * 32, sv);
+    ptx::tmem_ld_32x32_async(taddr + fabw::C_DP + c * 32, dv);
+    ptx::tmem_wait_ld32(sv);
+    ptx::tmem_wait_ld32(dv);
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 l4 = *reinterpret_cast<const float4*>(lse2 + c * 32 + i);
+      const float4 d4 = *reinterpret_cast<const float4*>(dlt + c * 32 + i);
+      const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float p = ex2(fmaf(sv[i + e], scale_log2, -ls[e]));
+        if (MASK) {
+          const int col = col0 + c * 32 + i + e;               // query column within the block
+          const bool ok = (col < qlim) && (!diag || col >= row);
+          p = ok ? p : 0.f;
+        }
+        sv[i + e] = p;
+        dv[i + e] = p * (dv[i + e] - ds[e]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      pk[c * 16 + i] = pack_bf16x2(sv[2 * i], sv[2 * i + 1]);
+      dk[c * 16 + i] = pack_bf16x2(dv[2 * i], dv[2 * i + 1]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(448, 1)
     attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_dy,
                        const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse,
                        const float* __restrict__ delta, __nv_bfloat16* __restrict__ dqkv, int Tn, int H,
-                       float scale, float scale_log2) {
+                       float scale, float scale_log2, long long* dbg) {
   using namespace fabw;
   using fatc::ex2;
   using fatc::sw128;
@@ -397,7 +436,7 @@ __global__ void __launch_bounds__(320, 1)
     ptx::mbar_init(sdp_full, 1);
     ptx::mbar_init(pds_full, 8);
     ptx::mbar_init(dq_full, 1);
-    ptx::mbar_init(dq_free, 8);
+    ptx::mbar_init(dq_free, 4);
     ptx::mbar_init(dkv_full, 1);
     ptx::fence_mbar_init();
   }
@@ -450,10 +489,13 @@ __global__ void __launch_bounds__(320, 1)
     ptx::mbar_wait(&qdo_full[0], 0);
     ptx::tc_fence_after();
     issue_sdp(0);
+    const bool recm = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
     for (int it = 0; it < nit; ++it) {
       const int s = it & 1;
+      if (recm) dbg[512 + 4 * it] = clock64();
       ptx::mbar_wait(pds_full, it & 1);
       ptx::tc_fence_after();
+      if (recm) dbg[512 + 4 * it + 1] = clock64();
       if (it + 1 < nit) {
         ptx::mbar_wait(&qdo_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
         ptx::tc_fence_after();
@@ -474,7 +516,9 @@ __global__ void __launch_bounds__(320, 1)
         }
       }
       __syncwarp();
+      if (recm) dbg[512 + 4 * it + 2] = clock64();
       if (it > 0) { ptx::mbar_wait(dq_free, (it - 1) & 1); ptx::tc_fence_after(); }
+      if (recm) dbg[512 + 4 * it + 3] = clock64();
       if (ptx::elect_one()) {
 #pragma unroll
         for (int k = 0; k < 8; ++k)    // K = 128 keys: 16 key rows = 2048 B per step for both operands
@@ -485,11 +529,45 @@ __global__ void __launch_bounds__(320, 1)
       }
       __syncwarp();
     }
+  } else if (warp >= 10) {
+    // ---- dQ write-back warps: TMEM (lane = query row) -> x scale -> swizzled smem -> TMA reduce-add ----
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;
+    const int et = threadIdx.x - 320;               // 0..127
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    for (int it = 0; it < nit; ++it) {
+      ptx::mbar_wait(dq_full, it & 1);
+      ptx::tc_fence_after();
+      float va[32], vb[32];
+      ptx::tmem_ld_32x32_async(tmem + lane_addr + C_DQ, va);
+      ptx::tmem_ld_32x32_async(tmem + lane_addr + C_DQ + 32, vb);
+      ptx::tmem_wait_ld32(va);
+      ptx::tmem_wait_ld32(vb);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(dq_free);
+      if (et == 0) ptx::bulk_wait_read<0>();        // both staging atoms drained
+      ptx::named_bar_sync(1, 128);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        *reinterpret_cast<float4*>(smem + OFF_DQ + sw128(row, i)) =
+            make_float4(va[4 * i] * scale, va[4 * i + 1] * scale, va[4 * i + 2] * scale, va[4 * i + 3] * scale);
+        *reinterpret_cast<float4*>(smem + OFF_DQ + TILE + sw128(row, i)) =
+            make_float4(vb[4 * i] * scale, vb[4 * i + 1] * scale, vb[4 * i + 2] * scale, vb[4 * i + 3] * scale);
+      }
+      ptx::fence_proxy_async();
+      ptx::named_bar_sync(1, 128);
+      if (et == 0) {
+        ptx::tma_reduce_add_2d(&tmap_dq, smem + OFF_DQ, h * HD, row_base + (jb + it) * BQ);
+        ptx::tma_reduce_add_2d(&tmap_dq, smem + OFF_DQ + TILE, h * HD + 32, row_base + (jb + it) * BQ);
+        ptx::bulk_commit();
+      }
+    }
+    if (et == 0) ptx::bulk_wait_all();
   } else {
     const int wg = (warp - 2) >> 2;                 // 0: query columns 0..63 of a block, 1: 64..127
     const int qd = warp & 3;
     const int row = qd * 32 + lane;                 // TMEM lane: key row (compute) / query row (dQ write-back)
-    const int et = (threadIdx.x - 64) & 127;
     const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
     const int key = jb * BKV + row;
     const float* lse_g = lse + (static_cast<size_t>(b) * H + h) * Tn;
@@ -500,28 +578,10 @@ __global__ void __launch_bounds__(320, 1)
       if (qg >= Tn) return 0.f;
       return ct < 128 ? lse_g[qg] * 1.4426950408889634f : del_g[qg];
     };
-    auto writeback_dq = [&](int it) {               // dQ of query block (jb+it): TMEM -> smem -> reduce-add
-      float v[32];
-      ptx::tmem_ld_32x32(tmem + lane_addr + C_DQ + wg * 32, v);
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(dq_free);
-      if (et == 0) ptx::bulk_wait_read<0>();        // the staging atom of this group is drained
-      ptx::named_bar_sync(1 + wg, 128);
-      uint8_t* stg = smem + OFF_DQ + wg * TILE;
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-        *reinterpret_cast<float4*>(stg + sw128(row, i)) =
-            make_float4(v[4 * i] * scale, v[4 * i + 1] * scale, v[4 * i + 2] * scale, v[4 * i + 3] * scale);
-      ptx::fence_proxy_async();
-      ptx::named_bar_sync(1 + wg, 128);
-      if (et == 0) {
-        ptx::tma_reduce_add_2d(&tmap_dq, stg, h * HD + wg * 32, row_base + (jb + it) * BQ);
-        ptx::bulk_commit();
-      }
-    };
     float st_next = load_stat(0);
+    const bool rec = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;
     for (int it = 0; it < nit; ++it) {
+      if (rec) dbg[8 * it] = clock64();
       // publish this block's statistics (prefetched one iteration ahead), fetch the next ones
       stat[(it & 1) * 256 + ct] = st_next;
       if (it + 1 < nit) st_next = load_stat(it + 1);
@@ -532,38 +592,16 @@ __global__ void __launch_bounds__(320, 1)
       const int qlim = Tn - (jb + it) * BQ;         // query columns >= qlim are padding
       ptx::mbar_wait(sdp_full, it & 1);
       ptx::tc_fence_after();
+      if (rec) dbg[8 * it + 1] = clock64();
       uint32_t pk[32], dk[32];                      // packed bf16 pairs of P^T and dS^T (64 columns)
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        float sv[32], dv[32];
-        ptx::tmem_ld_32x32_async(tmem + lane_addr + C_S + wg * 64 + c * 32, sv);
-        ptx::tmem_ld_32x32_async(tmem + lane_addr + C_DP + wg * 64 + c * 32, dv);
-        ptx::tmem_wait_ld32(sv);
-        ptx::tmem_wait_ld32(dv);
-#pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          const float4 l4 = *reinterpret_cast<const float4*>(lse2 + c * 32 + i);
-          const float4 d4 = *reinterpret_cast<const float4*>(dlt + c * 32 + i);
-          const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int col = wg * 64 + c * 32 + i + e;           // query column within the block
-            float p = ex2(fmaf(sv[i + e], scale_log2, -ls[e]));
-            const bool ok = (col < qlim) && (!diag || col >= row);
-            p = ok ? p : 0.f;
-            sv[i + e] = p;
-            dv[i + e] = p * (dv[i + e] - ds[e]);
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          pk[c * 16 + i] = pack_bf16x2(sv[2 * i], sv[2 * i + 1]);
-          dk[c * 16 + i] = pack_bf16x2(dv[2 * i], dv[2 * i + 1]);
-        }
-      }
+      // masking is needed only on the diagonal block and on a ragged last query block
+      if (diag || qlim < BQ) bwd_probs<true>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk);
+      else                   bwd_probs<false>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk);
       ptx::tc_fence_before();
+      if (rec) dbg[8 * it + 2] = clock64();
       // P^T / dS^T tiles are free once the previous block's dV/dK/dQ MMAs have retired
       if (it > 0) ptx::mbar_wait(dq_full, (it - 1) & 1);
+      if (rec) dbg[8 * it + 3] = clock64();
       uint8_t* pt = smem + OFF_PT + wg * TILE;
       uint8_t* dst = smem + OFF_DS + wg * TILE;
 #pragma unroll
@@ -574,11 +612,9 @@ __global__ void __launch_bounds__(320, 1)
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(pds_full);
-      if (it > 0) { ptx::tc_fence_after(); writeback_dq(it - 1); }
+      if (rec) dbg[8 * it + 4] = clock64();
+      if (rec) dbg[8 * it + 5] = clock64();
     }
-    ptx::mbar_wait(dq_full, (nit - 1) & 1);
-    ptx::tc_fence_after();
-    writeback_dq(nit - 1);
     // dK (group 0) / dV (group 1) of this key block
     ptx::mbar_wait(dkv_full, 0);
     ptx::tc_fence_after();
@@ -599,7 +635,6 @@ __global__ void __launch_bounds__(320, 1)
         }
       }
     }
-    if (et == 0) ptx::bulk_wait_all();
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -672,8 +707,8 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
       static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H);
   const dim3 grid(B * H, (T + BKV - 1) / BKV);
   const float scale = 1.0f / sqrtf(static_cast<float>(HD));
-  attn_bwd_tc_kernel<<<grid, 320, SMEM_BYTES, stream>>>(tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
-                                                        scale, scale * 1.4426950408889634f);
+  attn_bwd_tc_kernel<<<grid, 448, SMEM_BYTES, stream>>>(tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
+                                                        scale, scale * 1.4426950408889634f, g_attn_dbg);
   const size_t n8 = rows * C / 8;
   attn_dq_convert_kernel<<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, stream>>>(dq_acc, static_cast<__nv_bfloat16*>(dqkv), rows, C);
   count_launch(3);

@@ -1,0 +1,26 @@
+import torch
+from nanosandbox_b200 import _lib, ops
+lib = _lib.load()
+B, T, H, D = 12, 1024, 12, 64
+C = H * D
+qkv = torch.randn(B, T, 3 * C, device="cuda").to(torch.bfloat16)
+y = torch.empty(B, T, C, device="cuda", dtype=torch.bfloat16); dy = torch.randn_like(y)
+lse = torch.empty(B, H, T, device="cuda"); dqkv = torch.empty_like(qkv)
+delta = torch.empty(B, H, T, device="cuda"); dq_acc = torch.zeros(B * T, C, device="cuda")
+dbg = torch.zeros(1024 + 3 * 1152 + 16, dtype=torch.int64, device="cuda")
+ops.attention_fwd(qkv, y, lse, B, T, H, D)
+for _ in range(2):
+    ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc)
+lib.nsb_attention_debug_timing(dbg.data_ptr())
+ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc)
+torch.cuda.synchronize()
+lib.nsb_attention_debug_timing(None)
+d = dbg.cpu().tolist()
+t0 = d[0]
+print("compute warp per iteration: [top, sdp_full seen, P/dS in regs, dq_full(it-1) seen, stored+arrived, dQ written back]")
+for it in range(8):
+    r = [x - t0 for x in d[8 * it:8 * it + 6]]
+    print(it, r, "wait_sdp", r[1] - r[0], "compute", r[2] - r[1], "wait_dq", r[3] - r[2], "store", r[4] - r[3], "writeback", r[5] - r[4])
+print("mma warp per iteration: [top, pds_full seen, dV/dK issued, dq_free seen]")
+for it in range(8):
+    print(it, [x - t0 for x in d[512 + 4 * it:512 + 4 * it + 4]])
