@@ -195,6 +195,9 @@ def main():
     torch.cuda.set_device(dev)
     ddp = world > 1
     if ddp:
+        # keep stdout to the one JSON line (NCCL prints its version banner there at VERSION level)
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group(backend="nccl", device_id=dev)
     assert ACCUM_TOTAL % world == 0
     accum = ACCUM_TOTAL // world
@@ -321,7 +324,24 @@ def main():
         nbytes = model.buckets.bytes_reduced - b0
         t = torch.tensor([t_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        # stand-alone bus bandwidth of the same payload (one all-reduce over the whole bf16 staging arena)
+        stg = model.buckets.staging if model.buckets.staging is not None else model.buckets.grads
+        for _ in range(2):
+            dist.all_reduce(stg)
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(5):
+            dist.all_reduce(stg)
+        a1.record()
+        torch.cuda.synchronize()
+        alone = torch.tensor([a0.elapsed_time(a1) / 5], device=dev)
+        dist.all_reduce(alone, op=dist.ReduceOp.MAX)
+        sbytes = stg.numel() * stg.element_size()
         comm = {"bytes_per_rank_per_step": nbytes, "ms_on_comm_stream": t.item(),
+                "standalone_ms": alone.item(),
+                "standalone_busbw_GBps": sbytes * 2 * (world - 1) / world / (alone.item() / 1e3) / 1e9,
+
                 "busbw_GBps": nbytes * 2 * (world - 1) / world / (t.item() / 1e3) / 1e9,
                 "nominal_GBps": 900.0, "bucket_dtype": args.bucket_dtype}
         model.buckets.time_comm = False
