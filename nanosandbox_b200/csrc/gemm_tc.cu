@@ -315,12 +315,19 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         const TileCoord t = tile_of(w, num_m, num_n);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
+        const bool recm = dbg != nullptr && blockIdx.x == 0 && lane == 0;
+        const int ti = (w - unit) / nunits;
+        if (recm && ti < 60) dbg[1024 + 4 * ti] = clock64();          // tile start
         ptx::mbar_wait(&tempty[as], aphase ^ 1);
         ptx::tc_fence_after();
+        if (recm && ti < 60) dbg[1024 + 4 * ti + 1] = clock64();      // accumulator buffer free
+        long long waited = 0;
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(as * BN);
         for (int kb = kb0; kb < kb1; ++kb) {
+          const long long w0 = recm ? clock64() : 0;
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
+          if (recm) waited += clock64() - w0;
           const uint32_t a_addr = ptx::smem_u32(smem_a + stage * A_BYTES);
           const uint32_t b_addr = ptx::smem_u32(smem_b + stage * B_BYTES);
           // K-major:  rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused (1).
@@ -348,6 +355,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
           __syncwarp();
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
+        if (recm && ti < 60) { dbg[1024 + 4 * ti + 2] = clock64(); dbg[1024 + 4 * ti + 3] = waited; }  // issued; cycles waiting for operands
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }

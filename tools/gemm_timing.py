@@ -9,11 +9,18 @@ A = torch.randn(M, K, device="cuda").to(bf); B = torch.randn(N, K, device="cuda"
 cdt = torch.float32 if epi == E.EPI_RESIDUAL else bf
 C = torch.zeros(M, N, device="cuda", dtype=cdt); C2 = torch.zeros(M, N, device="cuda", dtype=bf)
 aux = torch.randn(M, N, device="cuda") if epi == E.EPI_RESIDUAL else None
-dbg = torch.zeros(1024, dtype=torch.int64, device="cuda")
+dbg = torch.zeros(4096, dtype=torch.int64, device="cuda")
 f = lambda: ops.gemm(M, N, K, A, K, True, B, K, True, C, N, epi, C2=C2 if epi == E.EPI_GELU else None, aux=aux)
 f(); f()
 lib.nsb_gemm_debug_timing(dbg.data_ptr()); f(); torch.cuda.synchronize(); lib.nsb_gemm_debug_timing(None)
-d = [x for x in dbg.cpu().tolist() if x != 0]
+full = dbg.cpu().tolist()
+m = full[1024:1024 + 240]
+print("MMA warp per tile: [start, acc free, all k-blocks issued] rel. clocks; wait-for-operands cycles")
+for i in range(0, 60):
+    r = m[4 * i:4 * i + 4]
+    if r[0] == 0: break
+    print(" tile", i, [x - m[0] for x in r[:3]], "tempty wait", r[1] - r[0], "mainloop", r[2] - r[1], "of which waiting for TMA", r[3])
+d = [x for x in full[:1000] if x != 0]
 t0 = d[0]
 rows = [d[i:i + 4] for i in range(0, len(d) - 3, 4)]
 for i, r in enumerate(rows[:40]):
