@@ -209,6 +209,46 @@ class GPT(nn.Module):
         self._acts = {}
         self.transformer.wpe.weight = nn.Parameter(self.transformer.wpe.weight.detach()[:block_size].clone())
 
+    @classmethod
+    def from_hf_state_dict(cls, sd_hf, config_args, verbose=False):
+        """Builds a GPT from a Hugging Face GPT-2 state dict: same key names as nanoGPT; the four Conv1D
+        weights (attn.c_attn, attn.c_proj, mlp.c_fc, mlp.c_proj) are stored transposed there."""
+        model = cls(GPTConfig(**config_args), verbose=verbose)
+        sd = model.state_dict()
+        transposed = ("attn.c_attn.weight", "attn.c_proj.weight", "mlp.c_fc.weight", "mlp.c_proj.weight")
+        keys_hf = [k for k in sd_hf if not k.endswith((".attn.masked_bias", ".attn.bias"))]
+        keys = [k for k in sd if not k.endswith(".attn.bias")]
+        assert len(keys_hf) == len(keys), f"mismatched keys: {len(keys_hf)} != {len(keys)}"
+        with torch.no_grad():
+            for k in keys_hf:
+                src = sd_hf[k].t() if k.endswith(transposed) else sd_hf[k]
+                assert src.shape == sd[k].shape, (k, tuple(src.shape), tuple(sd[k].shape))
+                sd[k].copy_(src)
+        return model
+
+    @classmethod
+    def from_pretrained(cls, model_type, override_args=None):
+        """nanoGPT's from_pretrained: loads OpenAI GPT-2 weights through the Hugging Face hub (needs the
+        weights in the local HF cache or network access)."""
+        assert model_type in {"gpt2", "gpt2-medium", "gpt2-large", "gpt2-xl"}
+        override_args = override_args or {}
+        assert all(k == "dropout" for k in override_args)
+        from transformers import GPT2LMHeadModel
+        config_args = {"gpt2": dict(n_layer=12, n_head=12, n_embd=768),
+                       "gpt2-medium": dict(n_layer=24, n_head=16, n_embd=1024),
+                       "gpt2-large": dict(n_layer=36, n_head=20, n_embd=1280),
+                       "gpt2-xl": dict(n_layer=48, n_head=25, n_embd=1600)}[model_type]
+        print("forcing vocab_size=50257, block_size=1024, bias=True")
+        config_args.update(vocab_size=50257, block_size=1024, bias=True)
+        if "dropout" in override_args:
+            config_args["dropout"] = override_args["dropout"]
+        try:
+            hf = GPT2LMHeadModel.from_pretrained(model_type)
+        except Exception as exc:
+            raise NsbError(f"from_pretrained({model_type!r}): the Hugging Face weights are not available "
+                           f"offline ({type(exc).__name__})") from exc
+        return cls.from_hf_state_dict(hf.state_dict(), config_args)
+
     def configure_optimizers(self, weight_decay, learning_rate, betas, device_type, verbose=True):
         from .optim import FusedAdamW
         if device_type != "cuda":

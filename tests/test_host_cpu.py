@@ -121,3 +121,21 @@ def test_entrypoint_derives_node_rank(tmp_path):
     r = subprocess.run(["bash", os.path.join(ROOT, "deploy", "entrypoint.sh"), "train.py"],
                        capture_output=True, text=True, env=env2)
     assert "--standalone --nproc_per_node=8 train.py" in r.stdout
+
+
+def test_from_hf_state_dict_mapping():
+    """HF GPT-2 (random init, no download) -> our GPT: same logits as the oracle given the same weights."""
+    tr = pytest.importorskip("transformers")
+    torch.manual_seed(0)
+    hf_cfg = tr.GPT2Config(vocab_size=97, n_positions=32, n_embd=64, n_layer=2, n_head=2,
+                           activation_function="gelu", resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
+    hf = tr.GPT2LMHeadModel(hf_cfg).eval()
+    args = dict(n_layer=2, n_head=2, n_embd=64, vocab_size=97, block_size=32, bias=True)
+    ours = GPT.from_hf_state_dict(hf.state_dict(), args)
+    ref = RefGPT(RefConfig(**args), verbose=False).eval()
+    ref.load_state_dict(ours.state_dict())
+    idx = torch.randint(0, 97, (2, 32))
+    with torch.no_grad():
+        a, _ = ref(idx, idx)
+        b = hf(idx).logits
+    assert torch.allclose(a, b, atol=1e-5, rtol=1e-5)

@@ -35,7 +35,7 @@ log_interval = 1
 eval_iters = 200
 eval_only = False
 always_save_checkpoint = True
-init_from = 'scratch'  # 'scratch' or 'resume'
+init_from = 'scratch'  # 'scratch', 'resume' or 'gpt2*'
 # wandb logging (accepted for CLI compatibility; not available offline)
 wandb_log = False
 wandb_project = 'owt'
@@ -75,6 +75,8 @@ synthetic_kind = 'uniform'  # 'uniform' (throughput) or 'markov' (learnable, los
 synthetic_vocab = 0      # 0: 65 for *_char datasets, else 50304
 bucket_dtype = 'bf16'    # gradient all-reduce payload: 'bf16' (cast+scale fused in the pack kernel) or 'fp32'
 peak_flops = 2.25e15     # B200 dense bf16 peak used for the second MFU figure in the log line
+tensorboard_log = False  # write loss / lr / tokens-per-second scalars (the reference mounts /data/runs for TensorBoard)
+tensorboard_dir = 'runs' # e.g. /data/runs/<job> in the k8s Jobs (/root/reference/README.md:83-87)
 # -----------------------------------------------------------------------------
 config_keys = [k for k, v in globals().items() if not k.startswith('_') and isinstance(v, (int, float, bool, str))]
 exec(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'configurator.py')).read())
@@ -171,9 +173,13 @@ elif init_from == 'resume':
     model.load_state_dict(state_dict)
     iter_num = checkpoint['iter_num']
     best_val_loss = checkpoint['best_val_loss']
+elif init_from.startswith('gpt2'):
+    print(f"Initializing from OpenAI GPT-2 weights: {init_from}")
+    model = GPT.from_pretrained(init_from, dict(dropout=dropout))  # needs the HF weights (cache or network)
+    for k in ['n_layer', 'n_head', 'n_embd', 'block_size', 'bias', 'vocab_size']:
+        model_args[k] = getattr(model.config, k)
 else:
-    raise SystemExit(f"init_from={init_from!r}: only 'scratch' and 'resume' are available offline "
-                     "(from_pretrained needs the Hugging Face hub)")
+    raise SystemExit(f"init_from={init_from!r}: expected 'scratch', 'resume' or 'gpt2*'")
 if block_size < model.config.block_size:
     model.crop_block_size(block_size)
     model_args['block_size'] = block_size
@@ -184,6 +190,11 @@ optimizer = model.configure_optimizers(weight_decay, learning_rate, (beta1, beta
 if checkpoint is not None:
     optimizer.load_state_dict(checkpoint['optimizer'])
 checkpoint = None
+
+tb_writer = None
+if tensorboard_log and master_process:
+    from torch.utils.tensorboard import SummaryWriter
+    tb_writer = SummaryWriter(log_dir=tensorboard_dir)
 
 raw_model = model
 if ddp:
@@ -228,6 +239,9 @@ while True:
     if iter_num % eval_interval == 0 and master_process:
         losses = estimate_loss()
         print(f"step {iter_num}: train loss {losses['train']:.4f}, val loss {losses['val']:.4f}")
+        if tb_writer is not None:
+            tb_writer.add_scalar("val/loss", float(losses['val']), iter_num)
+            tb_writer.add_scalar("train/eval_loss", float(losses['train']), iter_num)
         if losses['val'] < best_val_loss or always_save_checkpoint:
             best_val_loss = losses['val']
             if iter_num > 0:
@@ -263,10 +277,16 @@ while True:
         mfu_b200 = running_mfu * 312e12 * ddp_world_size / (peak_flops * ddp_world_size) if running_mfu > 0 else -1.0
         print(f"iter {iter_num}: loss {lossf:.4f}, time {dt*1000:.2f}ms, mfu {running_mfu*100:.2f}%"
               f" | {tokens_per_iter/dt:,.0f} tok/s, mfu_b200 {mfu_b200*100:.2f}%")
+        if tb_writer is not None:
+            tb_writer.add_scalar("train/loss", lossf, iter_num)
+            tb_writer.add_scalar("train/lr", lr, iter_num)
+            tb_writer.add_scalar("perf/tokens_per_sec", tokens_per_iter / dt, iter_num)
     iter_num += 1
     local_iter_num += 1
     if iter_num > max_iters:
         break
 
+if tb_writer is not None:
+    tb_writer.close()
 if ddp:
     destroy_process_group()
