@@ -7,6 +7,7 @@
 #include <atomic>
 
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 namespace nsb {
 
@@ -233,25 +234,157 @@ __global__ void __launch_bounds__(256, 2)
   }
 }
 
-// Stage 2: out[c] (+)= sum_p part[p][which][c].  grid (ceil(C/32), 2), block (32, 8)
-__global__ void __launch_bounds__(256)
+// Streaming variant of stage 1 (the one the launcher prefers): a producer warp keeps a ring of
+// 8-row slabs (dy, x, incoming residual gradient) in flight with bulk async copies
+// (cp.async.bulk + mbarrier), 8 consumer warps take one row each from shared memory.  Memory latency is
+// hidden by the ring instead of by occupancy; each consumer only holds its dw/db partials in registers.
+constexpr int kLnRows = 8;
+template <int NV, typename DyT, bool HAS_DB>
+__global__ void __launch_bounds__(288, 1)
+    layernorm_bwd_stream_kernel(const DyT* __restrict__ dy, const float* __restrict__ x,
+                                const float* __restrict__ w, const float* __restrict__ mean,
+                                const float* __restrict__ rstd, const float* __restrict__ dres_in,
+                                float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_lowp,
+                                float* __restrict__ part, int M, int C, int nstages) {
+  extern __shared__ __align__(128) uint8_t ln_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t dy_row = static_cast<uint32_t>(C) * sizeof(DyT), f_row = static_cast<uint32_t>(C) * 4u;
+  const uint32_t off_x = kLnRows * dy_row, off_r = off_x + kLnRows * f_row;
+  const uint32_t stage_bytes = off_r + (dres_in != nullptr ? kLnRows * f_row : 0u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ln_smem + static_cast<size_t>(nstages) * stage_bytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + 4;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < nstages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], kLnRows); }
+    ptx::fence_mbar_init();
+  }
+  __syncthreads();
+  const int ngroups = (M + kLnRows - 1) / kLnRows;
+  float4 dwacc[NV], dbacc[HAS_DB ? NV : 1];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) dwacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < (HAS_DB ? NV : 1); ++j) dbacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  if (warp == kLnRows) {
+    if (lane == 0) {
+      int it = 0;
+      for (int g = blockIdx.x; g < ngroups; g += gridDim.x, ++it) {
+        const int s = it % nstages;
+        ptx::mbar_wait(&empty[s], ((it / nstages) & 1) ^ 1);
+        const int row0 = g * kLnRows;
+        const uint32_t rows = static_cast<uint32_t>(min(kLnRows, M - row0));
+        uint8_t* st = ln_smem + static_cast<size_t>(s) * stage_bytes;
+        ptx::mbar_expect_tx(&full[s], rows * (dy_row + f_row + (dres_in != nullptr ? f_row : 0u)));
+        ptx::bulk_load_1d(st, dy + static_cast<size_t>(row0) * C, rows * dy_row, &full[s]);
+        ptx::bulk_load_1d(st + off_x, x + static_cast<size_t>(row0) * C, rows * f_row, &full[s]);
+        if (dres_in != nullptr)
+          ptx::bulk_load_1d(st + off_r, dres_in + static_cast<size_t>(row0) * C, rows * f_row, &full[s]);
+      }
+    }
+  } else {
+    const float invC = 1.0f / static_cast<float>(C);
+    int it = 0;
+    int g = blockIdx.x;
+    float mu_n = 0.f, rs_n = 0.f;
+    if (g < ngroups && g * kLnRows + warp < M) { mu_n = mean[g * kLnRows + warp]; rs_n = rstd[g * kLnRows + warp]; }
+    for (; g < ngroups; g += gridDim.x, ++it) {
+      const int s = it % nstages;
+      const int row = g * kLnRows + warp;
+      const float mu = mu_n, rs = rs_n;
+      const int gn = g + gridDim.x;                       // statistics of the next row, one iteration ahead
+      if (gn < ngroups && gn * kLnRows + warp < M) { mu_n = mean[gn * kLnRows + warp]; rs_n = rstd[gn * kLnRows + warp]; }
+      ptx::mbar_wait(&full[s], (it / nstages) & 1);
+      if (row < M) {
+        const uint8_t* st = ln_smem + static_cast<size_t>(s) * stage_bytes;
+        const DyT* sdy = reinterpret_cast<const DyT*>(st) + warp * C;
+        const float* sx = reinterpret_cast<const float*>(st + off_x) + warp * C;
+        const float* sr = reinterpret_cast<const float*>(st + off_r) + warp * C;
+        const size_t off = static_cast<size_t>(row) * C;
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+          const int c = (lane + 32 * j) * 4;
+          if (c < C) {
+            const float4 wv = __ldg(reinterpret_cast<const float4*>(w + c));
+            const float4 d = Vec4IO<DyT>::load(sdy + c);
+            const float4 xv = Vec4IO<float>::load(sx + c);
+            const float4 xh = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+            const float4 gg = make_float4(d.x * wv.x, d.y * wv.y, d.z * wv.z, d.w * wv.w);
+            s1 += (gg.x + gg.y) + (gg.z + gg.w);
+            s2 += (gg.x * xh.x + gg.y * xh.y) + (gg.z * xh.z + gg.w * xh.w);
+            dwacc[j].x += d.x * xh.x; dwacc[j].y += d.y * xh.y;
+            dwacc[j].z += d.z * xh.z; dwacc[j].w += d.w * xh.w;
+            if (HAS_DB) { dbacc[j].x += d.x; dbacc[j].y += d.y; dbacc[j].z += d.z; dbacc[j].w += d.w; }
+          }
+        }
+        const float c1 = warp_sum(s1) * invC, c2 = warp_sum(s2) * invC;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+          const int c = (lane + 32 * j) * 4;
+          if (c < C) {
+            const float4 wv = __ldg(reinterpret_cast<const float4*>(w + c));
+            const float4 d = Vec4IO<DyT>::load(sdy + c);
+            const float4 xv = Vec4IO<float>::load(sx + c);
+            const float4 xh = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+            float4 o = make_float4(rs * (d.x * wv.x - c1 - xh.x * c2), rs * (d.y * wv.y - c1 - xh.y * c2),
+                                   rs * (d.z * wv.z - c1 - xh.z * c2), rs * (d.w * wv.w - c1 - xh.w * c2));
+            if (dres_in != nullptr) {
+              const float4 r = Vec4IO<float>::load(sr + c);
+              o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+            }
+            Vec4IO<float>::store(dx + off + c, o);
+            if (dx_lowp != nullptr) Vec4IO<__nv_bfloat16>::store(dx_lowp + off + c, o);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&empty[s]);
+    }
+  }
+  // cross-warp reduction of the column partials (the staging ring is idle now and reused), dw then db
+  float* red = reinterpret_cast<float*>(ln_smem);
+  __syncthreads();
+#pragma unroll
+  for (int pass = 0; pass < (HAS_DB ? 2 : 1); ++pass) {
+    if (pass > 0) __syncthreads();
+    if (warp < kLnRows) {
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int c = (lane + 32 * j) * 4;
+        const float4 a = (pass == 0 || !HAS_DB) ? dwacc[j] : dbacc[HAS_DB ? j : 0];
+        if (c < 128 * NV) *reinterpret_cast<float4*>(&red[warp * 128 * NV + c]) = a;
+      }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < kLnRows; ++k) s += red[k * 128 * NV + c];
+      part[(static_cast<size_t>(blockIdx.x) * 2 + pass) * C + c] = s;
+    }
+  }
+}
+
+// Stage 2: out[c] (+)= sum_p part[p][which][c].  grid (ceil(C/32), 2), block (32, 32)
+__global__ void __launch_bounds__(1024)
     layernorm_bwd_reduce_kernel(const float* __restrict__ part, float* __restrict__ dw,
                                 float* __restrict__ db, int nparts, int C, int accumulate) {
-  __shared__ float red[8][33];
+  __shared__ float red[32][33];
   const int which = blockIdx.y;
   float* out = which == 0 ? dw : db;
   if (out == nullptr) return;
   const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
   if (c < C)
-    for (int p = threadIdx.y; p < nparts; p += 8)
+    for (int p = threadIdx.y; p < nparts; p += 32)
       s += part[(static_cast<size_t>(p) * 2 + which) * C + c];
   red[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
   if (threadIdx.y == 0 && c < C) {
     float t = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+    for (int k = 0; k < 32; ++k) t += red[k][threadIdx.x];
     out[c] = accumulate ? out[c] + t : t;
   }
 }
@@ -324,8 +457,22 @@ __global__ void __launch_bounds__(256)
   if (live) {
     const T* r = logits + static_cast<size_t>(row) * ld;
     if (VEC) {
+      const int nfull = V / EPV;             // vectors without a ragged edge: no per-element bounds checks
+      // two vectors per thread per trip: two independent 16-byte loads in flight
+      int i = t;
+      for (; i + TPR < nfull; i += 2 * TPR) {
+        float e[EPV], f[EPV];
+        RowVec<T>::load(r + i * EPV, e);
+        RowVec<T>::load(r + (i + TPR) * EPV, f);
+        float lm = fmaxf(e[0], f[0]);
+#pragma unroll
+        for (int k = 1; k < EPV; ++k) lm = fmaxf(lm, fmaxf(e[k], f[k]));
+        if (lm > m) { s *= ce_exp<T>(m - lm); m = lm; }
+#pragma unroll
+        for (int k = 0; k < EPV; ++k) s += ce_exp<T>(e[k] - m) + ce_exp<T>(f[k] - m);
+      }
       const int nvec = (V + EPV - 1) / EPV;
-      for (int i = t; i < nvec; i += TPR) {
+      for (; i < nvec; i += TPR) {
         float e[EPV];
         RowVec<T>::load(r + i * EPV, e);
         float lm = -INFINITY;
@@ -715,15 +862,42 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
   if (static_cast<size_t>(grid) * per_part > scratch_bytes) grid = static_cast<int>(scratch_bytes / per_part);
   NSB_REQUIRE(grid >= 1 && scratch != nullptr, "layernorm_bwd: scratch too small (%zu bytes)", scratch_bytes);
   const int nv = (C + 127) / 128;
+  // streaming kernel: rows must be bulk-copyable (row bytes % 16 == 0) and a ring of >= 2 slabs must fit
+  const size_t dy_row = static_cast<size_t>(C) * (dy_dtype == NSB_F32 ? 4 : 2);
+  const size_t slab = kLnRows * (dy_row + static_cast<size_t>(C) * 4 * (dres_in != nullptr ? 2 : 1));
+  int nstages = static_cast<int>((200 * 1024) / slab);
+  if (nstages > 4) nstages = 4;
+  const bool stream_ok = (dy_row % 16 == 0) && (C % 4 == 0) && nstages >= 2 && M >= 4 * kLnRows &&
+                         static_cast<size_t>(nstages) * slab >= static_cast<size_t>(kLnRows) * 128 * nv * 4;
+  if (stream_ok) {
+    int sgrid = (M + kLnRows - 1) / kLnRows;
+    if (sgrid > sm_count()) sgrid = sm_count();
+    if (sgrid > grid) sgrid = grid;
+    grid = sgrid;
+    const size_t smem = static_cast<size_t>(nstages) * slab + 64;
+#define NSB_LN_BWDS(TT, HASDB)                                                                          \
+  {                                                                                                     \
+    auto kern = layernorm_bwd_stream_kernel<NV, TT, HASDB>;                                             \
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 210 * 1024);                \
+    kern<<<grid, 288, smem, stream>>>(static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx,        \
+                                       static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C, nstages);   \
+  }
+    NSB_LN_DISPATCH(nv, {
+      if (dy_dtype == NSB_F32) { if (db != nullptr) NSB_LN_BWDS(float, true) else NSB_LN_BWDS(float, false) }
+      else { if (db != nullptr) NSB_LN_BWDS(__nv_bfloat16, true) else NSB_LN_BWDS(__nv_bfloat16, false) }
+    });
+#undef NSB_LN_BWDS
+  } else {
 #define NSB_LN_BWD(TT, HASDB)                                                                  \
   layernorm_bwd_kernel<NV, TT, HASDB><<<grid, 256, 0, stream>>>(                                \
       static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx, static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C)
-  NSB_LN_DISPATCH(nv, {
-    if (dy_dtype == NSB_F32) { if (db != nullptr) NSB_LN_BWD(float, true); else NSB_LN_BWD(float, false); }
-    else { if (db != nullptr) NSB_LN_BWD(__nv_bfloat16, true); else NSB_LN_BWD(__nv_bfloat16, false); }
-  });
+    NSB_LN_DISPATCH(nv, {
+      if (dy_dtype == NSB_F32) { if (db != nullptr) NSB_LN_BWD(float, true); else NSB_LN_BWD(float, false); }
+      else { if (db != nullptr) NSB_LN_BWD(__nv_bfloat16, true); else NSB_LN_BWD(__nv_bfloat16, false); }
+    });
 #undef NSB_LN_BWD
-  layernorm_bwd_reduce_kernel<<<dim3((C + 31) / 32, 2), dim3(32, 8), 0, stream>>>(
+  }
+  layernorm_bwd_reduce_kernel<<<dim3((C + 31) / 32, 2), dim3(32, 32), 0, stream>>>(
       scratch, dw, db, grid, C, accumulate);
   count_launch(2);
   return check_launch("layernorm_bwd");
