@@ -350,9 +350,10 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
 namespace fabw {
 constexpr int BQ = 128, BKV = 128, HD = 64;
 constexpr int TILE = 128 * 128;            // 16 KB: 128 rows x 128 B
-constexpr int OFF_K = 0, OFF_V = TILE, OFF_Q = 2 * TILE, OFF_DO = 4 * TILE;   // Q, dO: 2 stages each
-constexpr int OFF_PT = 6 * TILE, OFF_DS = 8 * TILE, OFF_DQ = 10 * TILE;       // 32 KB each
-constexpr int OFF_STAT = 12 * TILE;        // [2 stages][lse_log2 | delta][128] floats
+constexpr int QS = 3;                       // Q / dO ring depth
+constexpr int OFF_K = 0, OFF_V = TILE, OFF_Q = 2 * TILE, OFF_DO = (2 + QS) * TILE;
+constexpr int OFF_PT = (2 + 2 * QS) * TILE, OFF_DS = OFF_PT + 2 * TILE, OFF_DQ = OFF_DS + 2 * TILE;   // 32 KB each
+constexpr int OFF_STAT = OFF_DQ + 2 * TILE; // [2 stages][lse_log2 | delta][128] floats
 constexpr int OFF_BAR = OFF_STAT + 2 * 2 * 128 * 4;
 constexpr int SMEM_BYTES = OFF_BAR + 256;
 constexpr uint32_t TMEM_COLS = 512;
@@ -408,14 +409,15 @@ __global__ void __launch_bounds__(448, 1)
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* kv_full = bars;          // K, V landed
-  uint64_t* qdo_full = bars + 1;     // [2] Q_i, dO_i landed
-  uint64_t* qdo_empty = bars + 3;    // [2]
-  uint64_t* sdp_full = bars + 5;     // S^T, dP^T in TMEM
-  uint64_t* pds_full = bars + 6;     // P^T, dS^T in smem (and S^T/dP^T consumed)      count 8
-  uint64_t* dq_full = bars + 7;      // dV/dK/dQ MMAs of the block retired
-  uint64_t* dq_free = bars + 8;      // dQ columns read back                          count 8
-  uint64_t* dkv_full = bars + 9;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* qdo_full = bars + 1;     // [QS] Q_i, dO_i landed
+  uint64_t* qdo_empty = bars + 4;    // [QS]
+  uint64_t* sdp_full = bars + 7;     // S^T, dP^T in TMEM
+  uint64_t* pds_full = bars + 8;     // P^T, dS^T in smem                              count 8
+  uint64_t* dq_full = bars + 9;      // dV/dK/dQ MMAs of the block retired
+  uint64_t* dq_free = bars + 10;     // dQ columns read back                           count 4
+  uint64_t* dkv_full = bars + 11;
+  uint64_t* sdp_free = bars + 12;    // S^T / dP^T read into registers (TMEM columns reusable)  count 8
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
   float* stat = reinterpret_cast<float*>(smem + OFF_STAT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -432,12 +434,13 @@ __global__ void __launch_bounds__(448, 1)
     ptx::prefetch_tmap(&tmap_dy);
     ptx::prefetch_tmap(&tmap_dq);
     ptx::mbar_init(kv_full, 1);
-    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&qdo_full[s], 1); ptx::mbar_init(&qdo_empty[s], 1); }
+    for (int s = 0; s < QS; ++s) { ptx::mbar_init(&qdo_full[s], 1); ptx::mbar_init(&qdo_empty[s], 1); }
     ptx::mbar_init(sdp_full, 1);
     ptx::mbar_init(pds_full, 8);
     ptx::mbar_init(dq_full, 1);
     ptx::mbar_init(dq_free, 4);
     ptx::mbar_init(dkv_full, 1);
+    ptx::mbar_init(sdp_free, 8);
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
@@ -452,8 +455,8 @@ __global__ void __launch_bounds__(448, 1)
       ptx::tma_load_2d(smem + OFF_K, &tmap_qkv, kv_full, C + h * HD, row_base + jb * BKV);
       ptx::tma_load_2d(smem + OFF_V, &tmap_qkv, kv_full, 2 * C + h * HD, row_base + jb * BKV);
       for (int it = 0; it < nit; ++it) {
-        const int s = it & 1;
-        ptx::mbar_wait(&qdo_empty[s], ((it >> 1) & 1) ^ 1);
+        const int s = it % QS;
+        ptx::mbar_wait(&qdo_empty[s], ((it / QS) & 1) ^ 1);
         ptx::mbar_expect_tx(&qdo_full[s], 2 * TILE);
         ptx::tma_load_2d(smem + OFF_Q + s * TILE, &tmap_qkv, &qdo_full[s], h * HD, row_base + (jb + it) * BQ);
         ptx::tma_load_2d(smem + OFF_DO + s * TILE, &tmap_dy, &qdo_full[s], h * HD, row_base + (jb + it) * BQ);
@@ -471,7 +474,7 @@ __global__ void __launch_bounds__(448, 1)
     const uint64_t dDS = ptx::umma_smem_desc_sw128(sb + OFF_DS, 16, 1024);
     const uint64_t dDSmn = ptx::umma_smem_desc_sw128(sb + OFF_DS, TILE, 1024);       // A, MN-major (M = q), LBO = next 64 q
     auto issue_sdp = [&](int it) {
-      const int s = it & 1;
+      const int s = it % QS;
       const uint64_t q_k = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, 16, 1024);
       const uint64_t do_k = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, 16, 1024);
       if (ptx::elect_one()) {
@@ -491,16 +494,19 @@ __global__ void __launch_bounds__(448, 1)
     issue_sdp(0);
     const bool recm = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
     for (int it = 0; it < nit; ++it) {
-      const int s = it & 1;
+      const int s = it % QS;
       if (recm) dbg[512 + 4 * it] = clock64();
-      ptx::mbar_wait(pds_full, it & 1);
-      ptx::tc_fence_after();
-      if (recm) dbg[512 + 4 * it + 1] = clock64();
+      // next S^T / dP^T as soon as this block's have been read out (the compute warps are still
+      // writing P^T / dS^T to shared memory at that point)
       if (it + 1 < nit) {
-        ptx::mbar_wait(&qdo_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
+        ptx::mbar_wait(sdp_free, it & 1);
+        ptx::mbar_wait(&qdo_full[(it + 1) % QS], ((it + 1) / QS) & 1);
         ptx::tc_fence_after();
         issue_sdp(it + 1);
       }
+      ptx::mbar_wait(pds_full, it & 1);
+      ptx::tc_fence_after();
+      if (recm) dbg[512 + 4 * it + 1] = clock64();
       const uint64_t q_mn = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, TILE, 1024);   // B MN-major (N = d, K = q)
       const uint64_t do_mn = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, TILE, 1024);
       if (ptx::elect_one()) {
@@ -598,6 +604,8 @@ __global__ void __launch_bounds__(448, 1)
       if (diag || qlim < BQ) bwd_probs<true>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk);
       else                   bwd_probs<false>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk);
       ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(sdp_free);
       if (rec) dbg[8 * it + 2] = clock64();
       // P^T / dS^T tiles are free once the previous block's dV/dK/dQ MMAs have retired
       if (it > 0) ptx::mbar_wait(dq_full, (it - 1) & 1);

@@ -698,35 +698,50 @@ __global__ void __launch_bounds__(256) scale_f32_kernel(float* __restrict__ x, s
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) x[n4 * 4 + threadIdx.x] *= s;
 }
 // exact-erf GELU on bf16 activations (fp32 math inside), 8 elements per thread per step
+__device__ __forceinline__ uint4 gelu8(const uint4 u) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+  uint32_t o[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 x = unpack_bf16x2(w[k]);
+    o[k] = pack_bf16x2(gelu_fast(x.x), gelu_fast(x.y));
+  }
+  return make_uint4(o[0], o[1], o[2], o[3]);
+}
+__device__ __forceinline__ uint4 dgelu8(const uint4 g, const uint4 u) {
+  const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, hw[4] = {u.x, u.y, u.z, u.w};
+  uint32_t o[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 x = unpack_bf16x2(hw[k]), d = unpack_bf16x2(gw[k]);
+    o[k] = pack_bf16x2(d.x * gelu_fast_grad(x.x), d.y * gelu_fast_grad(x.y));
+  }
+  return make_uint4(o[0], o[1], o[2], o[3]);
+}
+// two 16-byte vectors per thread per trip (independent loads in flight)
 __global__ void __launch_bounds__(256)
     gelu_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ h, __nv_bfloat16* __restrict__ a, size_t n8) {
-  for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n8; i += static_cast<size_t>(gridDim.x) * 256) {
-    const uint4 u = ld_stream(h + i * 8);
-    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-    uint32_t o[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float2 x = unpack_bf16x2(w[k]);
-      o[k] = pack_bf16x2(gelu_fast(x.x), gelu_fast(x.y));
-    }
-    st_stream(a + i * 8, make_uint4(o[0], o[1], o[2], o[3]));
+  const size_t stride = static_cast<size_t>(gridDim.x) * 256;
+  size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+  for (; i + stride < n8; i += 2 * stride) {
+    const uint4 u0 = ld_stream(h + i * 8), u1 = ld_stream(h + (i + stride) * 8);
+    st_stream(a + i * 8, gelu8(u0));
+    st_stream(a + (i + stride) * 8, gelu8(u1));
   }
+  if (i < n8) st_stream(a + i * 8, gelu8(ld_stream(h + i * 8)));
 }
 // dh = dA * gelu'(h), in place over dA
 __global__ void __launch_bounds__(256)
     gelu_bwd_bf16_kernel(__nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ h, size_t n8) {
-  for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n8; i += static_cast<size_t>(gridDim.x) * 256) {
-    const uint4 g = ld_stream(da + i * 8);
-    const uint4 u = ld_stream(h + i * 8);
-    const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, hw[4] = {u.x, u.y, u.z, u.w};
-    uint32_t o[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float2 x = unpack_bf16x2(hw[k]), d = unpack_bf16x2(gw[k]);
-      o[k] = pack_bf16x2(d.x * gelu_fast_grad(x.x), d.y * gelu_fast_grad(x.y));
-    }
-    st_stream(da + i * 8, make_uint4(o[0], o[1], o[2], o[3]));
+  const size_t stride = static_cast<size_t>(gridDim.x) * 256;
+  size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+  for (; i + stride < n8; i += 2 * stride) {
+    const uint4 g0 = ld_stream(da + i * 8), u0 = ld_stream(h + i * 8);
+    const uint4 g1 = ld_stream(da + (i + stride) * 8), u1 = ld_stream(h + (i + stride) * 8);
+    st_stream(da + i * 8, dgelu8(g0, u0));
+    st_stream(da + (i + stride) * 8, dgelu8(g1, u1));
   }
+  if (i < n8) st_stream(da + i * 8, dgelu8(ld_stream(da + i * 8), ld_stream(h + i * 8)));
 }
 
 template <typename T>
