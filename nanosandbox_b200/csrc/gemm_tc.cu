@@ -172,12 +172,22 @@ __device__ __forceinline__ void epilogue_row32(const EpiParams& p, int m, int n,
 
 // ---- the kernel -------------------------------------------------------------------------------
 struct TileCoord { int m_blk, n_blk, split; };
-__device__ __forceinline__ TileCoord tile_of(int w, int num_m, int num_n) {
+// m-fastest walk: concurrently running tiles share the B panel, A panels stream (good when A fits
+// in L2 or is re-read few times).  n-fastest: the n-blocks of one A row-block run side by side, so
+// a huge A (the 1.2 GB dlogits in the lm_head gradient GEMMs) comes from HBM once.
+__device__ __forceinline__ TileCoord tile_of(int w, int num_m, int num_n, int n_fast) {
   TileCoord t;
-  t.m_blk = w % num_m;
-  const int rest = w / num_m;
-  t.n_blk = rest % num_n;
-  t.split = rest / num_n;
+  if (n_fast) {
+    t.n_blk = w % num_n;
+    const int rest = w / num_n;
+    t.m_blk = rest % num_m;
+    t.split = rest / num_m;
+  } else {
+    t.m_blk = w % num_m;
+    const int rest = w / num_m;
+    t.n_blk = rest % num_n;
+    t.split = rest / num_n;
+  }
   return t;
 }
 __device__ __forceinline__ uint32_t stg_off(int row, int q) {  // 16-byte chunk q of a 128-byte row
@@ -195,8 +205,8 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                    const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
                    const __grid_constant__ CUtensorMap tma_aux, int K, int num_m, int num_n, int splits,
-                   int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, EpiParams ep,
-                   long long* dbg) {
+                   int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, int n_fast,
+                   EpiParams ep, long long* dbg) {
   constexpr int BNL = BN / CG;                       // B rows staged by this CTA
   constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BNL * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN;
@@ -272,7 +282,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       constexpr int A_BOXES = A_MN ? BM / 64 : 1;
       constexpr int B_BOXES = B_MN ? BNL / 64 : 1;
       for (int w = unit; w < total_work; w += nunits) {
-        const TileCoord t = tile_of(w, num_m, num_n);
+        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
@@ -312,7 +322,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       int as = 0;
       uint32_t aphase = 0;
       for (int w = unit; w < total_work; w += nunits) {
-        const TileCoord t = tile_of(w, num_m, num_n);
+        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         const bool recm = dbg != nullptr && blockIdx.x == 0 && lane == 0;
@@ -376,7 +386,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       // ---- direct-store fallback (outputs whose row stride is not a multiple of 16 bytes) ----
       const bool use_atomics = (ep.kind == NSB_EPI_ACCUM) && splits > 1;
       for (int w = unit; w < total_work; w += nunits) {
-        const TileCoord t = tile_of(w, num_m, num_n);
+        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         ptx::mbar_wait(&tfull[as], aphase);
         ptx::tc_fence_after();
 #pragma unroll 1
@@ -420,7 +430,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         ++emit;
       };
       for (int w = unit; w < total_work; w += nunits) {
-        const TileCoord t = tile_of(w, num_m, num_n);
+        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         ptx::mbar_wait(&tfull[as], aphase);
         ptx::tc_fence_after();
         const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
@@ -595,7 +605,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       uint64_t* stgbar = staged + grp * nbuf;
       uint64_t* freebar = freeb + grp * nbuf;
       auto coords = [&](int chunk, int& col, int& rowg) {
-        const TileCoord t = tile_of(unit + (chunk / CHG) * nunits, num_m, num_n);
+        const TileCoord t = tile_of(unit + (chunk / CHG) * nunits, num_m, num_n, n_fast);
         col = t.n_blk * BN + ((chunk % CHG) * ngroups + grp) * CW;
         rowg = (t.m_blk * CG + static_cast<int>(rank)) * BM;
       };
@@ -715,7 +725,7 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint
 static long long* g_gemm_dbg = nullptr;
 struct LaunchPlan {
   CUtensorMap ta, tb, tc, tc2, taux;
-  int K, num_m, num_n, splits, kb_per_split, stages, nbuf, tma_epi, ngroups, aux_direct;
+  int K, num_m, num_n, splits, kb_per_split, stages, nbuf, tma_epi, ngroups, aux_direct, n_fast;
 };
 
 template <int BN, bool A_MN, bool B_MN, int CG, int NGRP = 2>
@@ -744,14 +754,14 @@ static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
-                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, ep, g_gemm_dbg);
+                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, lp.n_fast, ep, g_gemm_dbg);
   NSB_REQUIRE(e == cudaSuccess, "gemm_tc: launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("gemm_tc");
 }
 
 int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t stream, int force_bn, int force_splits,
-                   int force_direct_epi, int force_groups, int force_cg) {
+                   int force_direct_epi, int force_groups, int force_cg, int force_nfast) {
   const int M = a->M, N = a->N, K = a->K;
   int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
   if (force_bn == 128 || force_bn == 256) bn = force_bn;
@@ -788,6 +798,15 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   if (splits < 1) splits = 1;
   lp.splits = splits;
   lp.kb_per_split = kb_per_split;
+  // tile walk: keep the operand that would otherwise be re-streamed from HBM once per block of the
+  // other dimension (only matters when it does not fit in L2)
+  {
+    const double a_bytes = 2.0 * M * K, b_bytes = 2.0 * N * K, l2 = 100e6;
+    const double cost_mfast = (a_bytes > l2 ? a_bytes * lp.num_n : a_bytes) + b_bytes;
+    const double cost_nfast = a_bytes + (b_bytes > l2 ? b_bytes * lp.num_m : b_bytes);
+    lp.n_fast = cost_nfast < cost_mfast ? 1 : 0;
+    if (force_nfast >= 0) lp.n_fast = force_nfast;
+  }
 
   int rc;
   if (a->a_kmajor) rc = make_tmap_2d(&lp.ta, a->A, 2, K, M, a->lda, BK, BM);
@@ -859,7 +878,8 @@ int gemm_simt_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t s
 
 using namespace nsb;
 
-static int g_force_bn = 0, g_force_splits = 0, g_force_simt = 0, g_force_direct_epi = 0, g_force_groups = 0, g_force_cg = 0;
+static int g_force_bn = 0, g_force_splits = 0, g_force_simt = 0, g_force_direct_epi = 0, g_force_groups = 0, g_force_cg = 0,
+           g_force_nfast = -1;
 
 extern "C" {
 
@@ -873,6 +893,7 @@ void nsb_gemm_debug_config(int force_bn, int force_splits, int force_simt) {
   g_force_direct_epi = force_simt == 2;
   g_force_groups = force_simt == 3 ? 1 : (force_simt == 4 ? 2 : (force_simt == 7 ? 4 : 0));  // 3: one epilogue group, 4: two, 7: four (register stores)
   g_force_cg = force_simt == 5 ? 1 : (force_simt == 6 ? 2 : 0);      // 5: single-CTA tiles, 6: CTA pairs
+  g_force_nfast = force_simt == 8 ? 0 : (force_simt == 9 ? 1 : -1);   // 8: m-fastest tile walk, 9: n-fastest
 }
 
 // device buffer (>= 1024 int64) receiving clock64 stamps of CTA 0's first epilogue thread; NULL = off
@@ -892,7 +913,7 @@ int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
   ep.bias = a->bias; ep.alpha = a->alpha; ep.ldc = a->ldc; ep.c_bf16 = (a->c_dtype == NSB_BF16) ? 1 : 0;
   ep.accumulate = a->accumulate;
   if (a->in_dtype == NSB_F32 || g_force_simt) return gemm_simt_launch(a, ep, cs(stream));
-  return gemm_tc_launch(a, ep, cs(stream), g_force_bn, g_force_splits, g_force_direct_epi, g_force_groups, g_force_cg);
+  return gemm_tc_launch(a, ep, cs(stream), g_force_bn, g_force_splits, g_force_direct_epi, g_force_groups, g_force_cg, g_force_nfast);
 }
 
 }  // extern "C"

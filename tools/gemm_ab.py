@@ -16,12 +16,11 @@ def run(name, M, N, K, a_k, b_k, epi, acc, dbgs):
         lib.nsb_gemm_debug_config(0, 0, 0)
         out.append(f"dbg{d}: {t*1e3:6.1f} us")
     print(f"{name:22s}", "  ".join(out), flush=True)
-D = (0, 4, 5)   # default, two epilogue groups, single-CTA tiles
+D = (8, 9, 0)   # m-fastest, n-fastest, default heuristic
+V = 50304
+run("lm_head dgrad", Mt, Cc, V, True, False, E.EPI_STORE, False, D)
+run("lm_head wgrad", V, Cc, Mt, False, False, E.EPI_ACCUM, True, D)
+run("lm_head fwd", Mt, V, Cc, True, True, E.EPI_STORE, False, D)
 run("fc fwd store", Mt, 4*Cc, Cc, True, True, E.EPI_STORE, False, D)
-run("qkv fwd", Mt, 3*Cc, Cc, True, True, E.EPI_STORE, False, D)
-run("fc dgrad", Mt, Cc, 4*Cc, True, False, E.EPI_STORE, False, D)
-run("proj dgrad store", Mt, 4*Cc, Cc, True, False, E.EPI_STORE, False, D)
-run("mlp proj res", Mt, Cc, 4*Cc, True, True, E.EPI_RESIDUAL, False, (0, 5))
 run("fc wgrad", 4*Cc, Cc, Mt, False, False, E.EPI_ACCUM, True, D)
-run("qkv wgrad", 3*Cc, Cc, Mt, False, False, E.EPI_ACCUM, True, D)
-run("lm_head fwd", Mt, 50304, Cc, True, True, E.EPI_STORE, False, D)
+run("mlp proj res", Mt, Cc, 4*Cc, True, True, E.EPI_RESIDUAL, False, D)
