@@ -63,6 +63,7 @@ SIGNATURES = {
 DEBUG_SIGNATURES = {
     "nsb_gemm_debug_config": (None, [_I, _I, _I]),
     "nsb_gemm_debug_timing": (None, [_P]),
+    "nsb_gemm_debug_pdl": (None, [_I]),
     "nsb_attention_debug_config": (None, [_I]),
     "nsb_attention_debug_timing": (None, [_P]),
 }
@@ -85,6 +86,8 @@ def load() -> C.CDLL:
             fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
             fn.restype = res
             fn.argtypes = args
+    if os.environ.get("NSB_GEMM_PDL", "1") == "0":  # A/B switch for the dependent-launch overlap
+        lib.nsb_gemm_debug_pdl(0)
     _lib = lib
     return lib
 

@@ -173,6 +173,9 @@ __global__ void __launch_bounds__(192, 2)
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // barriers, TMEM and the descriptor prefetch above overlap the previous kernel's tail
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
 
   if (warp == 0) {
     if (lane == 0) {
@@ -322,7 +325,7 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
     attr_done = true;
   }
   const dim3 grid(B * H, (T + BQ - 1) / BQ);
-  attn_fwd_tc_kernel<<<grid, 192, SMEM_BYTES, stream>>>(tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
+  launch_pdl(attn_fwd_tc_kernel, dim3(grid), dim3(192), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
                                                         1.4426950408889634f / sqrtf(static_cast<float>(HD)), g_attn_dbg);
   count_launch();
   return check_launch("attention_fwd_tc");
@@ -448,6 +451,9 @@ __global__ void __launch_bounds__(448, 1)
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // barriers, TMEM and the descriptor prefetch above overlap the previous kernel's tail
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
 
   if (warp == 0) {
     if (lane == 0) {
@@ -652,6 +658,8 @@ __global__ void __launch_bounds__(448, 1)
 // dq (bf16, inside dqkv) = dq_acc (fp32); dq_acc is zeroed again for the next call
 __global__ void __launch_bounds__(256)
     attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, size_t M, int C) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t i = (static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x) * 8;
   if (i >= M * C) return;
   const size_t r = i / C, c = i % C;
@@ -667,6 +675,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     attn_delta_tc_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy,
                          float* __restrict__ delta, int B, int Tn, int H) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t g = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
   const size_t item = g >> 3;                       // (b*T + q) * H + h
   const int part = static_cast<int>(g & 7);
@@ -711,14 +721,14 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
     attr_done = true;
   }
   const size_t items = rows * H * 8;
-  attn_delta_tc_kernel<<<static_cast<unsigned>((items + 255) / 256), 256, 0, stream>>>(
+  launch_pdl(attn_delta_tc_kernel, dim3(static_cast<unsigned>((items + 255) / 256)), dim3(256), 0, stream, 
       static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H);
   const dim3 grid(B * H, (T + BKV - 1) / BKV);
   const float scale = 1.0f / sqrtf(static_cast<float>(HD));
-  attn_bwd_tc_kernel<<<grid, 448, SMEM_BYTES, stream>>>(tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
+  launch_pdl(attn_bwd_tc_kernel, dim3(grid), dim3(448), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
                                                         scale, scale * 1.4426950408889634f, g_attn_dbg);
   const size_t n8 = rows * C / 8;
-  attn_dq_convert_kernel<<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, stream>>>(dq_acc, static_cast<__nv_bfloat16*>(dqkv), rows, C);
+  launch_pdl(attn_dq_convert_kernel, dim3(static_cast<unsigned>((n8 + 255) / 256)), dim3(256), 0, stream, dq_acc, static_cast<__nv_bfloat16*>(dqkv), rows, C);
   count_launch(3);
   return check_launch("attention_bwd_tc");
 }

@@ -13,6 +13,27 @@ namespace nsb {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 int check_launch(const char* what);  // cudaGetLastError -> 0 / code (+ sets error text)
+bool pdl_enabled();                   // programmatic dependent launch switch (debug hook can turn it off)
+void set_pdl_enabled(bool on);
+
+// Launch with the programmatic-stream-serialization attribute: the grid may be scheduled while the
+// previous kernel in the stream drains (if that kernel executed pdl_trigger()); the kernel itself
+// must call pdl_wait() before its first global-memory access.
+template <typename... KArgs, typename... Args>
+static inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);  // errors surface in check_launch()
+}
 
 #define NSB_REQUIRE(cond, ...)        \
   do {                                \
@@ -93,6 +114,13 @@ __device__ __forceinline__ float gelu_fast_grad(float x) {
   const float cdf = gelu_fast_parts(x, e);
   return fmaf(x * 0.39894228040143267794f, e, cdf);
 }
+
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization
+// attribute may start (run its prologue) while the previous kernel in the stream drains, provided the
+// previous kernel signalled pdl_trigger(); pdl_wait() blocks until that kernel has completed and
+// its writes are visible.  Both are no-ops for plain launches.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // 128-bit streaming loads/stores (read-once data: keep it out of L1)
 __device__ __forceinline__ uint4 ld_stream(const void* p) {

@@ -20,6 +20,9 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+static std::atomic<int> g_pdl{1};
+bool pdl_enabled() { return g_pdl.load() != 0; }
+void set_pdl_enabled(bool on) { g_pdl.store(on ? 1 : 0); }
 void count_launch(int n) { g_launches.fetch_add(static_cast<unsigned long long>(n)); }
 int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
@@ -38,6 +41,8 @@ __global__ void __launch_bounds__(256) embedding_fwd_kernel(const int64_t* __res
                                                             const float4* __restrict__ wpe,
                                                             float4* __restrict__ x, int M, int T,
                                                             int C4) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<size_t>(M) * C4) return;
   const int row = static_cast<int>(i / C4), c = static_cast<int>(i % C4);
@@ -51,6 +56,8 @@ __global__ void __launch_bounds__(256) embedding_bwd_wte_kernel(const int64_t* _
                                                                 const float4* __restrict__ dx,
                                                                 float4* __restrict__ dwte, int M,
                                                                 int C4) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<size_t>(M) * C4) return;
   const int row = static_cast<int>(i / C4), c = static_cast<int>(i % C4);
@@ -61,6 +68,8 @@ __global__ void __launch_bounds__(256) embedding_bwd_wte_kernel(const int64_t* _
 __global__ void __launch_bounds__(256) embedding_bwd_wpe_kernel(const float4* __restrict__ dx,
                                                                 float4* __restrict__ dwpe, int B,
                                                                 int T, int C4, int accumulate) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<size_t>(T) * C4) return;
   float4 s = accumulate ? dwpe[i] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -104,6 +113,8 @@ __global__ void __launch_bounds__(256)
                          const float* __restrict__ b, OutT* __restrict__ y,
                          float* __restrict__ mean, float* __restrict__ rstd, int M, int C,
                          float eps) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= M) return;
@@ -160,6 +171,8 @@ __global__ void __launch_bounds__(256, 2)
                          const float* __restrict__ rstd, const float* __restrict__ dres_in,
                          float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_lowp,
                          float* __restrict__ part, int M, int C) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   __shared__ float red[8][128 * NV];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float4 dwacc[NV], dbacc[HAS_DB ? NV : 1];
@@ -246,6 +259,8 @@ __global__ void __launch_bounds__(288, 1)
                                 const float* __restrict__ rstd, const float* __restrict__ dres_in,
                                 float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_lowp,
                                 float* __restrict__ part, int M, int C, int nstages) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   extern __shared__ __align__(128) uint8_t ln_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t dy_row = static_cast<uint32_t>(C) * sizeof(DyT), f_row = static_cast<uint32_t>(C) * 4u;
@@ -370,6 +385,8 @@ __global__ void __launch_bounds__(288, 1)
 __global__ void __launch_bounds__(1024)
     layernorm_bwd_reduce_kernel(const float* __restrict__ part, float* __restrict__ dw,
                                 float* __restrict__ db, int nparts, int C, int accumulate) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   __shared__ float red[32][33];
   const int which = blockIdx.y;
   float* out = which == 0 ? dw : db;
@@ -448,6 +465,8 @@ __global__ void __launch_bounds__(256)
     cross_entropy_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ targets,
                              float* __restrict__ lse, float* __restrict__ row_loss, int M, int V,
                              int ld) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   constexpr int TPR = 256 / ROWS;  // threads per row
   constexpr int EPV = RowVec<T>::EPV;
   const int sub = threadIdx.x / TPR, t = threadIdx.x % TPR;
@@ -521,6 +540,8 @@ __global__ void __launch_bounds__(1024)
     cross_entropy_reduce_kernel(const float* __restrict__ row_loss,
                                 const int64_t* __restrict__ targets, float* __restrict__ stats,
                                 int M) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   __shared__ float ssum[32], scnt[32];
   float s = 0.f, n = 0.f;
   for (int i = threadIdx.x; i < M; i += 1024) {
@@ -541,6 +562,8 @@ __global__ void __launch_bounds__(256)
     cross_entropy_bwd_kernel(T* __restrict__ logits, const int64_t* __restrict__ targets,
                              const float* __restrict__ lse, const float* __restrict__ stats,
                              const float* __restrict__ gscale, int M, int V, int ld) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   constexpr int TPR = 256 / ROWS;
   constexpr int EPV = RowVec<T>::EPV;
   const int sub = threadIdx.x / TPR, t = threadIdx.x % TPR;
@@ -576,6 +599,8 @@ __global__ void __launch_bounds__(256)
 // =============================================================================================
 __global__ void __launch_bounds__(256)
     sumsq_partial_kernel(const float* __restrict__ g, size_t n, float* __restrict__ part) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   __shared__ float red[8];
   float s = 0.f;
   const size_t n4 = n / 4;
@@ -601,6 +626,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(1024)
     clip_coef_kernel(const float* __restrict__ part, int nparts, float max_norm,
                      float* __restrict__ out) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   __shared__ double red[32];
   double s = 0.0;
   for (int i = threadIdx.x; i < nparts; i += 1024) s += static_cast<double>(part[i]);
@@ -626,6 +653,8 @@ __global__ void __launch_bounds__(256)
                  const uint8_t* __restrict__ chunk_decay, float beta1, float beta2, float eps,
                  float decay_factor, float step_size, float bc2_sqrt,
                  const float* __restrict__ gscale) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t i = (static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x) * 4;
   const float gs = gscale ? *gscale : 1.f;
   const float df = chunk_decay[blockIdx.x] ? decay_factor : 1.f;
@@ -660,6 +689,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, size_t n,
                          float scale) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t n8 = n / 8;
   for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n8;
        i += static_cast<size_t>(gridDim.x) * 256) {
@@ -675,6 +706,8 @@ __global__ void __launch_bounds__(256)
 }
 __global__ void __launch_bounds__(256)
     cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict__ out, size_t n) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t n8 = n / 8;
   for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n8;
        i += static_cast<size_t>(gridDim.x) * 256) {
@@ -688,6 +721,8 @@ __global__ void __launch_bounds__(256)
     out[n8 * 8 + threadIdx.x] = __bfloat162float(in[n8 * 8 + threadIdx.x]);
 }
 __global__ void __launch_bounds__(256) scale_f32_kernel(float* __restrict__ x, size_t n, float s) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t n4 = n / 4;
   for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n4;
        i += static_cast<size_t>(gridDim.x) * 256) {
@@ -721,6 +756,8 @@ __device__ __forceinline__ uint4 dgelu8(const uint4 g, const uint4 u) {
 // two 16-byte vectors per thread per trip (independent loads in flight)
 __global__ void __launch_bounds__(256)
     gelu_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ h, __nv_bfloat16* __restrict__ a, size_t n8) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t stride = static_cast<size_t>(gridDim.x) * 256;
   size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
   for (; i + stride < n8; i += 2 * stride) {
@@ -733,6 +770,8 @@ __global__ void __launch_bounds__(256)
 // dh = dA * gelu'(h), in place over dA
 __global__ void __launch_bounds__(256)
     gelu_bwd_bf16_kernel(__nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ h, size_t n8) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   const size_t stride = static_cast<size_t>(gridDim.x) * 256;
   size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
   for (; i + stride < n8; i += 2 * stride) {
@@ -748,6 +787,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
     colsum_kernel(const T* __restrict__ dy, int ld, float* __restrict__ db, int accumulate, int M,
                   int N) {
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
   __shared__ float red[8][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
@@ -793,7 +834,7 @@ int nsb_embedding_fwd(const int64_t* idx, const float* wte, const float* wpe, fl
   const int M = B * T, C4 = C / 4;
   const size_t total = static_cast<size_t>(M) * C4;
   if (total == 0) return 0;
-  embedding_fwd_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, cs(stream)>>>(
+  launch_pdl(embedding_fwd_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0, cs(stream), 
       idx, reinterpret_cast<const float4*>(wte), reinterpret_cast<const float4*>(wpe),
       reinterpret_cast<float4*>(x), M, T, C4);
   count_launch();
@@ -808,10 +849,10 @@ int nsb_embedding_bwd(const int64_t* idx, const float* dx, float* dwte, float* d
   const int M = B * T, C4 = C / 4;
   const size_t total = static_cast<size_t>(M) * C4;
   if (total == 0) return 0;
-  embedding_bwd_wte_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, cs(stream)>>>(
+  launch_pdl(embedding_bwd_wte_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0, cs(stream), 
       idx, reinterpret_cast<const float4*>(dx), reinterpret_cast<float4*>(dwte), M, C4);
   const size_t tp = static_cast<size_t>(T) * C4;
-  embedding_bwd_wpe_kernel<<<static_cast<unsigned>((tp + 255) / 256), 256, 0, cs(stream)>>>(
+  launch_pdl(embedding_bwd_wpe_kernel, dim3(static_cast<unsigned>((tp + 255) / 256)), dim3(256), 0, cs(stream), 
       reinterpret_cast<const float4*>(dx), reinterpret_cast<float4*>(dwpe), B, T, C4,
       accumulate_wpe);
   count_launch(2);
@@ -839,10 +880,10 @@ int nsb_layernorm_fwd(const float* x, const float* w, const float* b, void* y, i
   const unsigned grid = (M + 7) / 8;
   NSB_LN_DISPATCH(nv, {
     if (y_dtype == NSB_F32)
-      layernorm_fwd_kernel<NV, float><<<grid, 256, 0, cs(stream)>>>(
+      launch_pdl(layernorm_fwd_kernel<NV, float>, dim3(grid), dim3(256), 0, cs(stream), 
           x, w, b, static_cast<float*>(y), mean, rstd, M, C, eps);
     else
-      layernorm_fwd_kernel<NV, __nv_bfloat16><<<grid, 256, 0, cs(stream)>>>(
+      launch_pdl(layernorm_fwd_kernel<NV, __nv_bfloat16>, dim3(grid), dim3(256), 0, cs(stream), 
           x, w, b, static_cast<__nv_bfloat16*>(y), mean, rstd, M, C, eps);
   });
   count_launch();
@@ -894,7 +935,7 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
   {                                                                                                     \
     auto kern = layernorm_bwd_stream_kernel<NV, TT, HASDB>;                                             \
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 210 * 1024);                \
-    kern<<<grid, 288, smem, stream>>>(static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx,        \
+    launch_pdl(kern, dim3(grid), dim3(288), smem, stream, static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx,        \
                                        static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C, nstages);   \
   }
     NSB_LN_DISPATCH(nv, {
@@ -904,7 +945,7 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
 #undef NSB_LN_BWDS
   } else {
 #define NSB_LN_BWD(TT, HASDB)                                                                  \
-  layernorm_bwd_kernel<NV, TT, HASDB><<<grid, 256, 0, stream>>>(                                \
+  launch_pdl(layernorm_bwd_kernel<NV, TT, HASDB>, dim3(grid), dim3(256), 0, stream,                                 \
       static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx, static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C)
     NSB_LN_DISPATCH(nv, {
       if (dy_dtype == NSB_F32) { if (db != nullptr) NSB_LN_BWD(float, true); else NSB_LN_BWD(float, false); }
@@ -912,7 +953,7 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
     });
 #undef NSB_LN_BWD
   }
-  layernorm_bwd_reduce_kernel<<<dim3((C + 31) / 32, 2), dim3(32, 32), 0, stream>>>(
+  launch_pdl(layernorm_bwd_reduce_kernel, dim3(dim3((C + 31) / 32, 2)), dim3(dim3(32, 32)), 0, stream, 
       scratch, dw, db, grid, C, accumulate);
   count_launch(2);
   return check_launch("layernorm_bwd");
@@ -938,7 +979,7 @@ int nsb_cross_entropy_fwd(const void* logits, int dtype, const int64_t* targets,
   const bool small = V <= 2048;
   const unsigned grid = small ? (M + 7) / 8 : M;
 #define CE_FWD(TT, ROWS, VEC)                                                     \
-  cross_entropy_fwd_kernel<TT, ROWS, VEC><<<grid, 256, 0, cs(stream)>>>(          \
+  launch_pdl(cross_entropy_fwd_kernel<TT, ROWS, VEC>, dim3(grid), dim3(256), 0, cs(stream),           \
       static_cast<const TT*>(logits), targets, lse, row_loss, M, V, ld)
   if (dtype == NSB_F32) {
     if (small) { if (vec) CE_FWD(float, 8, true); else CE_FWD(float, 8, false); }
@@ -948,7 +989,7 @@ int nsb_cross_entropy_fwd(const void* logits, int dtype, const int64_t* targets,
     else       { if (vec) CE_FWD(__nv_bfloat16, 1, true); else CE_FWD(__nv_bfloat16, 1, false); }
   }
 #undef CE_FWD
-  cross_entropy_reduce_kernel<<<1, 1024, 0, cs(stream)>>>(row_loss, targets, stats, M);
+  launch_pdl(cross_entropy_reduce_kernel, dim3(1), dim3(1024), 0, cs(stream), row_loss, targets, stats, M);
   count_launch(2);
   return check_launch("cross_entropy_fwd");
 }
@@ -964,7 +1005,7 @@ int nsb_cross_entropy_bwd(void* logits, int dtype, const int64_t* targets, const
   const bool small = V <= 2048;
   const unsigned grid = small ? (M + 7) / 8 : M;
 #define CE_BWD(TT, ROWS, VEC)                                                     \
-  cross_entropy_bwd_kernel<TT, ROWS, VEC><<<grid, 256, 0, cs(stream)>>>(          \
+  launch_pdl(cross_entropy_bwd_kernel<TT, ROWS, VEC>, dim3(grid), dim3(256), 0, cs(stream),           \
       static_cast<TT*>(logits), targets, lse, stats, gscale, M, V, ld)
   if (dtype == NSB_F32) {
     if (small) { if (vec) CE_BWD(float, 8, true); else CE_BWD(float, 8, false); }
@@ -988,8 +1029,8 @@ int grad_clip_coef_launch(const float* g, size_t n, float max_norm, float* scrat
   int grid = norm_grid(n);
   if (static_cast<size_t>(grid) * sizeof(float) > scratch_bytes) grid = static_cast<int>(scratch_bytes / sizeof(float));
   NSB_REQUIRE(grid >= 1 && scratch != nullptr, "grad_clip_coef: scratch too small (%zu bytes)", scratch_bytes);
-  sumsq_partial_kernel<<<grid, 256, 0, stream>>>(g, n, scratch);
-  clip_coef_kernel<<<1, 1024, 0, stream>>>(scratch, grid, max_norm, out);
+  launch_pdl(sumsq_partial_kernel, dim3(grid), dim3(256), 0, stream, g, n, scratch);
+  launch_pdl(clip_coef_kernel, dim3(1), dim3(1024), 0, stream, scratch, grid, max_norm, out);
   count_launch(2);
   return check_launch("grad_clip_coef");
 }
@@ -1007,7 +1048,7 @@ int nsb_adamw_step(float* p, const float* g, float* m, float* v, void* p_lowp,
   NSB_REQUIRE(n % 1024 == 0, "adamw_step: arena length %zu is not a multiple of 1024", n);
   NSB_REQUIRE(aligned16(p) && aligned16(g) && aligned16(m) && aligned16(v), "adamw_step: unaligned arena");
   if (n == 0) return 0;
-  adamw_kernel<<<static_cast<unsigned>(n / 1024), 256, 0, cs(stream)>>>(
+  launch_pdl(adamw_kernel, dim3(static_cast<unsigned>(n / 1024)), dim3(256), 0, cs(stream), 
       p, g, m, v, static_cast<__nv_bfloat16*>(p_lowp), chunk_decay, beta1, beta2, eps,
       decay_factor, step_size, bc2_sqrt, gscale);
   count_launch();
@@ -1017,7 +1058,7 @@ int nsb_adamw_step(float* p, const float* g, float* m, float* v, void* p_lowp,
 int nsb_cast_f32_to_bf16(const float* in, void* out, size_t n, float scale, nsb_stream_t stream) {
   NSB_REQUIRE(aligned16(in) && aligned16(out), "cast_f32_to_bf16: unaligned pointer");
   if (n == 0) return 0;
-  cast_f32_bf16_kernel<<<grid_for(n / 8, 256 * 4, 8 * sm_count()), 256, 0, cs(stream)>>>(
+  launch_pdl(cast_f32_bf16_kernel, dim3(grid_for(n / 8, 256 * 4, 8 * sm_count())), dim3(256), 0, cs(stream), 
       in, static_cast<__nv_bfloat16*>(out), n, scale);
   count_launch();
   return check_launch("cast_f32_to_bf16");
@@ -1025,7 +1066,7 @@ int nsb_cast_f32_to_bf16(const float* in, void* out, size_t n, float scale, nsb_
 int nsb_cast_bf16_to_f32(const void* in, float* out, size_t n, nsb_stream_t stream) {
   NSB_REQUIRE(aligned16(in) && aligned16(out), "cast_bf16_to_f32: unaligned pointer");
   if (n == 0) return 0;
-  cast_bf16_f32_kernel<<<grid_for(n / 8, 256 * 4, 8 * sm_count()), 256, 0, cs(stream)>>>(
+  launch_pdl(cast_bf16_f32_kernel, dim3(grid_for(n / 8, 256 * 4, 8 * sm_count())), dim3(256), 0, cs(stream), 
       static_cast<const __nv_bfloat16*>(in), out, n);
   count_launch();
   return check_launch("cast_bf16_to_f32");
@@ -1033,14 +1074,14 @@ int nsb_cast_bf16_to_f32(const void* in, float* out, size_t n, nsb_stream_t stre
 int nsb_scale_f32(float* x, size_t n, float scale, nsb_stream_t stream) {
   NSB_REQUIRE(aligned16(x), "scale_f32: unaligned pointer");
   if (n == 0) return 0;
-  scale_f32_kernel<<<grid_for(n / 4, 256 * 4, 8 * sm_count()), 256, 0, cs(stream)>>>(x, n, scale);
+  launch_pdl(scale_f32_kernel, dim3(grid_for(n / 4, 256 * 4, 8 * sm_count())), dim3(256), 0, cs(stream), x, n, scale);
   count_launch();
   return check_launch("scale_f32");
 }
 int nsb_gelu_fwd_bf16(const void* h, void* a, size_t n, nsb_stream_t stream) {
   NSB_REQUIRE(n % 8 == 0 && aligned16(h) && aligned16(a), "gelu_fwd_bf16: need 16-byte aligned buffers and n %% 8 == 0");
   if (n == 0) return 0;
-  gelu_fwd_bf16_kernel<<<grid_for(n / 8, 256 * 2, 16 * sm_count()), 256, 0, cs(stream)>>>(
+  launch_pdl(gelu_fwd_bf16_kernel, dim3(grid_for(n / 8, 256 * 2, 16 * sm_count())), dim3(256), 0, cs(stream), 
       static_cast<const __nv_bfloat16*>(h), static_cast<__nv_bfloat16*>(a), n / 8);
   count_launch();
   return check_launch("gelu_fwd_bf16");
@@ -1048,7 +1089,7 @@ int nsb_gelu_fwd_bf16(const void* h, void* a, size_t n, nsb_stream_t stream) {
 int nsb_gelu_bwd_bf16(void* da, const void* h, size_t n, nsb_stream_t stream) {
   NSB_REQUIRE(n % 8 == 0 && aligned16(h) && aligned16(da), "gelu_bwd_bf16: need 16-byte aligned buffers and n %% 8 == 0");
   if (n == 0) return 0;
-  gelu_bwd_bf16_kernel<<<grid_for(n / 8, 256 * 2, 16 * sm_count()), 256, 0, cs(stream)>>>(
+  launch_pdl(gelu_bwd_bf16_kernel, dim3(grid_for(n / 8, 256 * 2, 16 * sm_count())), dim3(256), 0, cs(stream), 
       static_cast<__nv_bfloat16*>(da), static_cast<const __nv_bfloat16*>(h), n / 8);
   count_launch();
   return check_launch("gelu_bwd_bf16");
@@ -1059,9 +1100,9 @@ int nsb_colsum(const void* dy, int dtype, int ld, float* db, int accumulate, int
   if (N == 0) return 0;
   const dim3 grid((N + 31) / 32), block(32, 8);
   if (dtype == NSB_F32)
-    colsum_kernel<float><<<grid, block, 0, cs(stream)>>>(static_cast<const float*>(dy), ld, db, accumulate, M, N);
+    launch_pdl(colsum_kernel<float>, dim3(grid), dim3(block), 0, cs(stream), static_cast<const float*>(dy), ld, db, accumulate, M, N);
   else
-    colsum_kernel<__nv_bfloat16><<<grid, block, 0, cs(stream)>>>(static_cast<const __nv_bfloat16*>(dy), ld, db, accumulate, M, N);
+    launch_pdl(colsum_kernel<__nv_bfloat16>, dim3(grid), dim3(block), 0, cs(stream), static_cast<const __nv_bfloat16*>(dy), ld, db, accumulate, M, N);
   count_launch();
   return check_launch("colsum");
 }

@@ -271,6 +271,10 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
   if (CG == 2) ptx::cluster_sync();                   // peer barriers initialised before any remote signal
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above (barriers, TMEM, descriptor prefetch) may overlap the previous kernel's tail;
+  // from here on we touch global memory
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     // ================================ TMA producer ==========================================
@@ -746,13 +750,15 @@ static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_
   cfg.blockDim = dim3(64 + 160 * NGRP);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
                                      lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, lp.n_fast, ep, g_gemm_dbg);
   NSB_REQUIRE(e == cudaSuccess, "gemm_tc: launch failed: %s", cudaGetErrorString(e));
@@ -897,6 +903,9 @@ void nsb_gemm_debug_config(int force_bn, int force_splits, int force_simt) {
 }
 
 // device buffer (>= 1024 int64) receiving clock64 stamps of CTA 0's first epilogue thread; NULL = off
+// 0 disables programmatic dependent launch for every kernel of the library (prologue overlap with the
+// previous kernel's tail)
+void nsb_gemm_debug_pdl(int enable) { nsb::set_pdl_enabled(enable != 0); }
 void nsb_gemm_debug_timing(void* device_buffer) { nsb::g_gemm_dbg = static_cast<long long*>(device_buffer); }
 
 int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
