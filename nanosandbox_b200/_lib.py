@@ -64,6 +64,7 @@ DEBUG_SIGNATURES = {
     "nsb_gemm_debug_config": (None, [_I, _I, _I]),
     "nsb_gemm_debug_timing": (None, [_P]),
     "nsb_gemm_debug_pdl": (None, [_I]),
+    "nsb_gemm_debug_pipeline": (None, [_I, _I, _I]),
     "nsb_attention_debug_config": (None, [_I]),
     "nsb_attention_debug_timing": (None, [_P]),
 }

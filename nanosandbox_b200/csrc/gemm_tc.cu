@@ -206,7 +206,17 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
                    const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
                    const __grid_constant__ CUtensorMap tma_aux, int K, int num_m, int num_n, int splits,
                    int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, int n_fast,
-                   EpiParams ep, long long* dbg) {
+                   int pipe_epi, EpiParams ep, long long* dbg) {
+  // per-CTA wall-clock trace (debug buffer of >= 8192 words): ns since boot at 8 points of the CTA's life
+  auto gstamp_if = [&](bool who, int slot) {
+    if (dbg != nullptr && who) {
+      unsigned long long gt;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+      dbg[4096 + 8 * blockIdx.x + slot] = static_cast<long long>(gt);
+    }
+  };
+  auto gstamp = [&](int slot) { gstamp_if(threadIdx.x == 0, slot); };
+  gstamp(0);
   constexpr int BNL = BN / CG;                       // B rows staged by this CTA
   constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BNL * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN;
@@ -273,8 +283,10 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
   const uint32_t tmem_base = *tmem_slot;
   // everything above (barriers, TMEM, descriptor prefetch) may overlap the previous kernel's tail;
   // from here on we touch global memory
+  gstamp(1);
   pdl_wait();
   pdl_trigger();
+  gstamp(2);
 
   if (warp == 0) {
     // ================================ TMA producer ==========================================
@@ -331,7 +343,12 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         const bool recm = dbg != nullptr && blockIdx.x == 0 && lane == 0;
         const int ti = (w - unit) / nunits;
-        if (recm && ti < 60) dbg[1024 + 4 * ti] = clock64();          // tile start
+        if (recm && ti < 60) {
+          dbg[1024 + 4 * ti] = clock64();                              // tile start
+          unsigned long long gt;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+          dbg[2048 + ti] = static_cast<long long>(gt);                 // same instant in ns (effective SM clock)
+        }
         ptx::mbar_wait(&tempty[as], aphase ^ 1);
         ptx::tc_fence_after();
         if (recm && ti < 60) dbg[1024 + 4 * ti + 1] = clock64();      // accumulator buffer free
@@ -342,6 +359,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
           if (recm) waited += clock64() - w0;
+          if (w == unit && kb == kb0) gstamp_if(lane == 0, 4);          // first operands landed
           const uint32_t a_addr = ptx::smem_u32(smem_a + stage * A_BYTES);
           const uint32_t b_addr = ptx::smem_u32(smem_b + stage * B_BYTES);
           // K-major:  rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused (1).
@@ -372,6 +390,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         if (recm && ti < 60) { dbg[1024 + 4 * ti + 2] = clock64(); dbg[1024 + 4 * ti + 3] = waited; }  // issued; cycles waiting for operands
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
+      gstamp_if(lane == 0, 5);                                          // all MMAs issued
     }
   } else if (warp >= 2) {
     // ================================ epilogue ==============================================
@@ -404,6 +423,135 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
+    } else if (pipe_epi && ep.kind != NSB_EPI_GELU && ep.kind != NSB_EPI_DGELU) {
+      // ---- staged epilogue, software-pipelined (plain store / residual add / accumulation) ----
+      // The tile is drained in 32-column units with two register sets: the TMEM load of unit u+1 is
+      // in flight while unit u is converted and written to the staging buffer, and the accumulator
+      // buffer goes back to the MMA warp as soon as the last load has landed in registers.  A
+      // staging buffer is one unit (fp32 outputs, 128-byte rows of 32 floats) or two (bf16, 64
+      // columns); the group's store warp ships it exactly as in the path below.
+      const bool c32 = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_ACCUM || !ep.c_bf16);
+      const bool aux_tma = (ep.kind == NSB_EPI_RESIDUAL) && !aux_direct;
+      const bool has_bias = ep.bias != nullptr && ep.kind != NSB_EPI_ACCUM;
+      const bool scaled = alpha != 1.f;
+      const int UPT = BN / 32 / ngroups;              // units per tile for this group (even)
+      uint8_t* pool = smem_stg + grp * nbuf * STG_BYTES;
+      uint64_t* auxbar = auxfull + grp * nbuf;
+      uint64_t* stgbar = staged + grp * nbuf;
+      uint64_t* freebar = freeb + grp * nbuf;
+      const bool rec = dbg != nullptr && blockIdx.x == 0 && hw_warp == 0 && lane == 0;
+      int nrec = 0;
+      auto stamp = [&]() { if (rec && nrec < 1000) dbg[nrec++] = clock64(); };
+      int slot = 0;                                   // staging buffer of the next emission
+      uint32_t useph = 0;                             // parity of that buffer's use count
+      uint8_t* buf = nullptr;
+      auto acquire = [&]() {
+        if (aux_tma) ptx::mbar_wait(&auxbar[slot], useph);      // the aux tile landing doubles as "buffer free"
+        else ptx::mbar_wait(&freebar[slot], useph ^ 1);
+        buf = pool + slot * STG_BYTES;
+      };
+      auto publish = [&]() {
+        ptx::fence_proxy_async();
+        ptx::mbar_arrive(&stgbar[slot]);
+        if (++slot == nbuf) { slot = 0; useph ^= 1; }
+      };
+      const uint32_t lane_bits = static_cast<uint32_t>(q * 32) << 16;
+      auto unit_col = [&](int u) -> int {             // first column (within the tile) of unit u
+        return c32 ? (grp + u * ngroups) * 32 : (grp + (u >> 1) * ngroups) * 64 + (u & 1) * 32;
+      };
+      for (int w = unit; w < total_work; w += nunits) {
+        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
+        const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
+        const uint32_t tbase = tmem_base + lane_bits + static_cast<uint32_t>(as * BN);
+        auto process = [&](int u, float* v) {
+          const int n0 = t.n_blk * BN + unit_col(u);
+          if (c32 || (u & 1) == 0) acquire();
+          stamp();                                  // [1] accumulators + buffer ready
+          if (scaled) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= alpha;
+          }
+          if (has_bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += (n0 + j < ep.N) ? __ldg(ep.bias + n0 + j) : 0.f;
+          }
+          if (c32) {
+            if (ep.kind == NSB_EPI_RESIDUAL) {
+              float4 a[8];
+              if (aux_tma) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[j] = *reinterpret_cast<const float4*>(buf + stg_off(row, j));
+              } else {
+                const float* rs = static_cast<const float*>(ep.aux) + static_cast<size_t>(m0 + row) * ep.ldc;
+                const bool rok = m0 + row < ep.M;
+                if (rok && n0 + 32 <= ep.N) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) a[j] = __ldg(reinterpret_cast<const float4*>(rs + n0) + j);
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) {
+                    a[j].x = (rok && n0 + 4 * j + 0 < ep.N) ? rs[n0 + 4 * j + 0] : 0.f;
+                    a[j].y = (rok && n0 + 4 * j + 1 < ep.N) ? rs[n0 + 4 * j + 1] : 0.f;
+                    a[j].z = (rok && n0 + 4 * j + 2 < ep.N) ? rs[n0 + 4 * j + 2] : 0.f;
+                    a[j].w = (rok && n0 + 4 * j + 3 < ep.N) ? rs[n0 + 4 * j + 3] : 0.f;
+                  }
+                }
+              }
+              if (ep.c_bf16) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  v[4 * j] = a[j].x + round_bf16(v[4 * j]); v[4 * j + 1] = a[j].y + round_bf16(v[4 * j + 1]);
+                  v[4 * j + 2] = a[j].z + round_bf16(v[4 * j + 2]); v[4 * j + 3] = a[j].w + round_bf16(v[4 * j + 3]);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  v[4 * j] += a[j].x; v[4 * j + 1] += a[j].y; v[4 * j + 2] += a[j].z; v[4 * j + 3] += a[j].w;
+                }
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *reinterpret_cast<float4*>(buf + stg_off(row, j)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            stamp();                                // [2] staged
+            publish();
+          } else {
+            const int h4 = (u & 1) * 4;             // this unit's half of the 128-byte staging row
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<uint4*>(buf + stg_off(row, h4 + j)) =
+                  make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                             pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+            stamp();                                // [2] staged
+            if (u & 1) publish();
+          }
+          stamp();                                  // [3] published
+        };
+        ptx::mbar_wait(&tfull[as], aphase);
+        ptx::tc_fence_after();
+        float x[32], y[32];
+        ptx::tmem_ld_32x32_async(tbase + static_cast<uint32_t>(unit_col(0)), x);
+#pragma unroll 1
+        for (int u = 0; u < UPT; u += 2) {
+          stamp();                                  // [0] unit start
+          ptx::tmem_wait_ld32(x);
+          ptx::tmem_ld_32x32_async(tbase + static_cast<uint32_t>(unit_col(u + 1)), y);
+          process(u, x);
+          stamp();                                  // [0] unit start
+          ptx::tmem_wait_ld32(y);
+          if (u + 2 < UPT) {
+            ptx::tmem_ld_32x32_async(tbase + static_cast<uint32_t>(unit_col(u + 2)), x);
+          } else {
+            // every accumulator of this tile is in registers: hand the TMEM buffer back before staging
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
+          }
+          process(u + 1, y);
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+      gstamp(6);                                                        // last unit staged
     } else {
       // ---- staged epilogue: TMEM -> registers -> swizzled smem; the group's store warp ships it ----
       const bool c32 = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_ACCUM || !ep.c_bf16);
@@ -586,6 +734,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
+      gstamp(6);                                                        // last chunk staged
     }
   }
   if (warp == -1 && tma_epi) {
@@ -624,7 +773,9 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         for (int j = 0; j < nbuf && j < total_chunks; ++j) load_aux(j);
       }
       __syncwarp();
-      const int inflight = nbuf - 2;         // stores allowed to be still reading their buffer
+      // stores allowed to be still reading their buffer; with aux tiles a buffer is refilled as early as
+      // possible (the refill is the look-ahead of the aux stream: nbuf - inflight chunks)
+      const int inflight = aux_tma ? (nbuf >= 6 ? 2 : 1) : (nbuf > 4 ? 2 : nbuf - 2);
       for (int e = 0; e < total_emit; ++e) {
         const int b = e % nbuf;
         ptx::mbar_wait(&stgbar[b], (e / nbuf) & 1);
@@ -636,7 +787,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
           else ptx::tma_store_2d(map, pool + b * STG_BYTES, col, rowg);
           ptx::bulk_commit();
           if (e >= inflight) {
-            if (inflight == 1) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<2>();
+            if (inflight <= 0) ptx::bulk_wait_read<0>(); else if (inflight == 1) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<2>();
             const int done = e - inflight;    // this emission's buffer has been read out
             if (aux_tma) { if (done + nbuf < total_chunks) load_aux(done + nbuf); }
             else ptx::mbar_arrive(&freebar[done % nbuf]);
@@ -644,8 +795,9 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         }
         __syncwarp();
       }
-      if (ptx::elect_one()) ptx::bulk_wait_all();
+      if (ptx::elect_one()) ptx::bulk_wait_read<0>();   // smem may be released once the stores have read it
       __syncwarp();
+      gstamp_if(grp == 0 && lane == 0, 7);
     }
   }
 
@@ -656,6 +808,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
     if (CG == 2) ptx::tmem_dealloc_pair(tmem_base, TMEM_COLS);
     else ptx::tmem_dealloc(tmem_base, TMEM_COLS);
   }
+  gstamp(3);
 }
 
 // ---- host: tensor maps --------------------------------------------------------------------------
@@ -727,9 +880,10 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint
 }
 
 static long long* g_gemm_dbg = nullptr;
+static int g_force_nbuf = 0, g_force_stages = 0, g_pipe_epi = 1;   // debug: staging buffers per group / operand ring depth
 struct LaunchPlan {
   CUtensorMap ta, tb, tc, tc2, taux;
-  int K, num_m, num_n, splits, kb_per_split, stages, nbuf, tma_epi, ngroups, aux_direct, n_fast;
+  int K, num_m, num_n, splits, kb_per_split, stages, nbuf, tma_epi, ngroups, aux_direct, n_fast, pipe_epi;
 };
 
 template <int BN, bool A_MN, bool B_MN, int CG, int NGRP = 2>
@@ -760,7 +914,7 @@ static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
-                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, lp.n_fast, ep, g_gemm_dbg);
+                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, lp.n_fast, lp.pipe_epi, ep, g_gemm_dbg);
   NSB_REQUIRE(e == cudaSuccess, "gemm_tc: launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("gemm_tc");
@@ -848,12 +1002,14 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   // and the residual add (whose fp32 aux tile arrives by TMA into the staging buffers) run on one group,
   // which leaves more shared memory to the operand ring.
   lp.ngroups = ((heavy && force_groups != 1) || (tma_epi && force_groups == 2)) ? 2 : 1;
-  if (ep.kind == NSB_EPI_RESIDUAL) lp.ngroups = 1;
+  if (ep.kind == NSB_EPI_RESIDUAL && force_groups != 2) lp.ngroups = 1;
   // GELU backward with two groups reads its pre-activation tile straight from global (no room for
   // aux staging buffers next to the output buffers of two groups)
   lp.aux_direct = (ep.kind == NSB_EPI_DGELU && lp.ngroups == 2) ? 1 : 0;
-  lp.nbuf = tma_epi ? ((has_aux && !lp.aux_direct) ? 4 : (lp.ngroups == 2 ? 3 : 4)) : 0;
-  int stages = kMaxStages;
+  lp.nbuf = tma_epi ? (lp.ngroups == 2 ? 3 : 4) : 0;
+  lp.pipe_epi = g_pipe_epi;
+  if (tma_epi && g_force_nbuf >= 2) lp.nbuf = g_force_nbuf;
+  int stages = g_force_stages > 0 ? g_force_stages : kMaxStages;
   while (stages > 2 && smem_bytes_for(bn / cg, stages, lp.nbuf * lp.ngroups) > kSmemLimit) --stages;
   lp.stages = stages;
 
@@ -906,6 +1062,12 @@ void nsb_gemm_debug_config(int force_bn, int force_splits, int force_simt) {
 // 0 disables programmatic dependent launch for every kernel of the library (prologue overlap with the
 // previous kernel's tail)
 void nsb_gemm_debug_pdl(int enable) { nsb::set_pdl_enabled(enable != 0); }
+// nbuf/stages: 0 = policy default; pipe_epi < 0 keeps the current setting (1 = software-pipelined epilogue)
+void nsb_gemm_debug_pipeline(int nbuf, int stages, int pipe_epi) {
+  nsb::g_force_nbuf = nbuf;
+  nsb::g_force_stages = stages;
+  if (pipe_epi >= 0) nsb::g_pipe_epi = pipe_epi;
+}
 void nsb_gemm_debug_timing(void* device_buffer) { nsb::g_gemm_dbg = static_cast<long long*>(device_buffer); }
 
 int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
