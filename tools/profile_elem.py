@@ -19,3 +19,9 @@ for _ in range(2):
     ops.cross_entropy_fwd(logits, tg, ls, rl, st, V)
 torch.cuda.synchronize()
 print("ok")
+hh = torch.randn(Mt, 4 * Cc, device=DEV).to(torch.bfloat16); aa = torch.empty_like(hh)
+for _ in range(2):
+    ops.gelu_fwd(hh, aa)
+    ops.gelu_bwd(aa, hh)
+torch.cuda.synchronize()
+print("ok2")
