@@ -85,6 +85,15 @@ int nsb_cross_entropy_bwd(void* logits, int dtype, const int64_t* targets, const
                           const float* stats, const float* gscale, int M, int V, int ld,
                           nsb_stream_t stream);
 
+/* K9+K9': both passes in one kernel for bf16 logits whose row (ld * 2 bytes) fits in shared memory:
+ * the row is read from HBM once.  Same lse / row_loss / stats as nsb_cross_entropy_fwd; logits <-
+ * softmax(logits) - onehot(target), 0 for ignored rows and for columns V..ld-1, NOT scaled: the caller
+ * multiplies by gscale / stats[1] downstream (the alpha of the two GEMMs that read it).  Fails with a
+ * message for fp32 logits, rows that are not 16-byte aligned, or rows that do not fit. */
+int nsb_cross_entropy_fwd_bwd(void* logits, int dtype, const int64_t* targets, float* lse,
+                              float* row_loss, float* stats, int M, int V, int ld,
+                              nsb_stream_t stream);
+
 /* K12: global L2 norm of a flat fp32 gradient arena and the clip coefficient
  * min(1, max_norm / (norm + 1e-6)).  Replaces clip_grad_norm_ (torch/nn/utils/clip_grad.py:
  * 96-106, 165-174).  out[0] = total norm, out[1] = coefficient (applied inside nsb_adamw_step). */

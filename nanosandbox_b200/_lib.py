@@ -45,6 +45,7 @@ SIGNATURES = {
     "nsb_layernorm_bwd": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _Z, _I, _I, _P]),
     "nsb_layernorm_bwd_noalloc": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "nsb_cross_entropy_fwd": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "nsb_cross_entropy_fwd_bwd": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _P]),
     "nsb_cross_entropy_bwd": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _P]),
     "nsb_grad_norm_scratch_bytes": (_Z, [_Z]),
     "nsb_grad_clip_coef": (_I, [_P, _Z, _F, _P, _Z, _P, _P]),

@@ -367,7 +367,8 @@ constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
 // returned as packed bf16 pairs.  MASK: causal mask on the diagonal block / padding columns.
 template <bool MASK>
 __device__ __forceinline__ void bwd_probs(uint32_t taddr, const float* lse2, const float* dlt, float scale_log2,
-                                          int col0, int row, int qlim, bool diag, uint32_t* pk, uint32_t* dk) {
+                                          int col0, int row, int qlim, bool diag, uint32_t* pk, uint32_t* dk,
+                                          long long* trace = nullptr) {
   using fatc::ex2;
 #pragma unroll
   for (int c = 0; c < 2; ++c) {
@@ -376,6 +377,7 @@ __device__ __forceinline__ void bwd_probs(uint32_t taddr, const float* lse2, con
     ptx::tmem_ld_32x32_async(taddr + fabw::C_DP + c * 32, dv);
     ptx::tmem_wait_ld32(sv);
     ptx::tmem_wait_ld32(dv);
+    if (trace != nullptr) trace[2 * c] = clock64() + (__float_as_int(sv[0]) & 0) + (__float_as_int(dv[31]) & 0);
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
       const float4 l4 = *reinterpret_cast<const float4*>(lse2 + c * 32 + i);
@@ -398,6 +400,7 @@ __device__ __forceinline__ void bwd_probs(uint32_t taddr, const float* lse2, con
       pk[c * 16 + i] = pack_bf16x2(sv[2 * i], sv[2 * i + 1]);
       dk[c * 16 + i] = pack_bf16x2(dv[2 * i], dv[2 * i + 1]);
     }
+    if (trace != nullptr) trace[2 * c + 1] = clock64() + (pk[c * 16 + 15] & 0) + (dk[c * 16] & 0);
   }
 }
 
@@ -607,8 +610,9 @@ __global__ void __launch_bounds__(448, 1)
       if (rec) dbg[8 * it + 1] = clock64();
       uint32_t pk[32], dk[32];                      // packed bf16 pairs of P^T and dS^T (64 columns)
       // masking is needed only on the diagonal block and on a ragged last query block
-      if (diag || qlim < BQ) bwd_probs<true>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk);
-      else                   bwd_probs<false>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk);
+      long long* tr = rec ? dbg + 256 + 4 * it : nullptr;   // [tmem 0 landed, math 0 done, tmem 1 landed, math 1 done]
+      if (diag || qlim < BQ) bwd_probs<true>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk, tr);
+      else                   bwd_probs<false>(tmem + lane_addr + wg * 64, lse2, dlt, scale_log2, wg * 64, row, qlim, diag, pk, dk, tr);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(sdp_free);

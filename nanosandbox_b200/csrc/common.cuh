@@ -93,17 +93,21 @@ __device__ __forceinline__ float gelu_exact_grad(float x) {
 
 // Fast variants for bf16 outputs (rounded to 8 mantissa bits afterwards): erf by Abramowitz-Stegun
 // 7.1.26 (|error| < 1.5e-7) sharing one exp with the Gaussian density.
+__device__ __forceinline__ float mufu_rcp(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float mufu_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// Phi(x) = 0.5 (1 + erf(x / sqrt 2)); the 0.5 is folded into the polynomial, the two special-function
+// evaluations are the bare MUFU instructions (their arguments are in range: 1 <= 1 + p z, -x^2/2 <= 0)
 __device__ __forceinline__ float gelu_fast_parts(float x, float& pdf_unscaled) {
   const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-  const float e = __expf(-z * z);  // = exp(-x^2 / 2)
-  float p = fmaf(t, 1.061405429f, -1.453152027f);
-  p = fmaf(t, p, 1.421413741f);
-  p = fmaf(t, p, -0.284496736f);
-  p = fmaf(t, p, 0.254829592f);
-  const float erf_abs = 1.0f - p * t * e;
+  const float t = mufu_rcp(fmaf(0.3275911f, z, 1.0f));
+  const float e = mufu_ex2((x * x) * -0.72134752044448170368f);  // exp(-x^2 / 2) = 2^(-x^2 log2(e) / 2)
+  float p = fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f);
+  p = fmaf(t, p, 0.5f * 1.421413741f);
+  p = fmaf(t, p, 0.5f * -0.284496736f);
+  p = fmaf(t, p, 0.5f * 0.254829592f);
+  const float half_erf_abs = fmaf(-(p * t), e, 0.5f);
   pdf_unscaled = e;
-  return 0.5f * (1.0f + copysignf(erf_abs, x));  // Phi(x)
+  return 0.5f + copysignf(half_erf_abs, x);  // Phi(x)
 }
 __device__ __forceinline__ float gelu_fast(float x) {
   float e;

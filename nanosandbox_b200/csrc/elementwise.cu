@@ -594,6 +594,144 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Fused forward + backward for bf16 logits whose row fits in shared memory (one CTA per row, two
+// resident CTAs per SM): the row comes from HBM once (bulk async copies in four pieces), max, log-sum-
+// exp and the loss are computed from shared memory, and softmax - onehot goes straight back over the
+// logits.  HBM traffic: one read + one write of the logits instead of two reads + one write.
+// The gradient is left UNSCALED (the caller folds gscale / n_valid into the GEMMs that consume it).
+constexpr int kCeFusedThreads = 512;
+constexpr int kCeFusedPieces = 4;
+__global__ void __launch_bounds__(kCeFusedThreads, 2)
+    cross_entropy_fused_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ targets,
+                               float* __restrict__ lse, float* __restrict__ row_loss, int V, int ld) {
+  extern __shared__ __align__(128) uint8_t ce_smem[];
+  __shared__ uint64_t bars[kCeFusedPieces];
+  __shared__ float red[kCeFusedThreads / 32];
+  __shared__ float bcast[2];
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  __nv_bfloat16* grow = logits + static_cast<size_t>(row) * ld;
+  const int nvec = ld / 8;                                   // 16-byte vectors per row (ld % 8 == 0)
+  const int pv = (nvec + kCeFusedPieces - 1) / kCeFusedPieces;
+  if (tid == 0) {
+    for (int p = 0; p < kCeFusedPieces; ++p) ptx::mbar_init(&bars[p], 1);
+    ptx::fence_mbar_init();
+  }
+  __syncthreads();
+  pdl_wait();
+  pdl_trigger();
+  if (tid == 0) {
+    for (int p = 0; p < kCeFusedPieces; ++p) {
+      const int v0 = p * pv, v1 = min(nvec, v0 + pv);
+      if (v1 > v0) {
+        const uint32_t bytes = static_cast<uint32_t>(v1 - v0) * 16u;
+        ptx::mbar_expect_tx(&bars[p], bytes);
+        ptx::bulk_load_1d(ce_smem + static_cast<size_t>(v0) * 16, grow + static_cast<size_t>(v0) * 8, bytes, &bars[p]);
+      } else {
+        ptx::mbar_arrive(&bars[p]);
+      }
+    }
+  }
+  const int64_t tg = targets[row];
+  const uint4* srow = reinterpret_cast<const uint4*>(ce_smem);
+  const int nfull = V / 8;                                   // vectors entirely inside the V valid columns
+  // ---- pass 1: row maximum (packed bf16 max; piece p is consumed as soon as it has landed)
+  __nv_bfloat162 mx2 = __float2bfloat162_rn(-INFINITY);
+  float mtail = -INFINITY;
+  for (int p = 0; p < kCeFusedPieces; ++p) {
+    ptx::mbar_wait(&bars[p], 0);
+    const int v1 = min(nvec, (p + 1) * pv);
+    for (int i = p * pv + tid; i < v1; i += kCeFusedThreads) {
+      const uint4 u = srow[i];
+      if (i < nfull) {
+        const __nv_bfloat162 a = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&u.x), *reinterpret_cast<const __nv_bfloat162*>(&u.y));
+        const __nv_bfloat162 b = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&u.z), *reinterpret_cast<const __nv_bfloat162*>(&u.w));
+        mx2 = __hmax2(mx2, __hmax2(a, b));
+      } else {
+        const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&u);
+        for (int k = 0; k < 8; ++k)
+          if (i * 8 + k < V) mtail = fmaxf(mtail, __bfloat162float(e[k]));
+      }
+    }
+  }
+  float m = fmaxf(fmaxf(__low2float(mx2), __high2float(mx2)), mtail);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (lane == 0) red[warp] = m;
+  __syncthreads();
+  if (warp == 0) {
+    float v = lane < kCeFusedThreads / 32 ? red[lane] : -INFINITY;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (lane == 0) bcast[0] = v;
+  }
+  __syncthreads();
+  m = bcast[0];
+  if (m == -INFINITY) m = 0.f;
+  constexpr float kLog2e = 1.4426950408889634f;
+  auto ex2 = [](float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; };
+  // ---- pass 2: sum of exp(x - max)
+  const float mneg = -m * kLog2e;
+  float s = 0.f;
+  for (int i = tid; i < nvec; i += kCeFusedThreads) {
+    const uint4 u = srow[i];
+    if (i < nfull) {
+      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      s += (ex2(fmaf(a.x, kLog2e, mneg)) + ex2(fmaf(a.y, kLog2e, mneg))) + (ex2(fmaf(b.x, kLog2e, mneg)) + ex2(fmaf(b.y, kLog2e, mneg))) +
+           (ex2(fmaf(c.x, kLog2e, mneg)) + ex2(fmaf(c.y, kLog2e, mneg))) + (ex2(fmaf(d.x, kLog2e, mneg)) + ex2(fmaf(d.y, kLog2e, mneg)));
+    } else {
+      const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&u);
+      for (int k = 0; k < 8; ++k)
+        if (i * 8 + k < V) s += ex2(fmaf(__bfloat162float(e[k]), kLog2e, mneg));
+    }
+  }
+  s = warp_sum(s);
+  if (lane == 0) red[warp] = s;
+  __syncthreads();
+  if (warp == 0) {
+    float v = lane < kCeFusedThreads / 32 ? red[lane] : 0.f;
+    v = warp_sum(v);
+    if (lane == 0) bcast[1] = v;
+  }
+  __syncthreads();
+  s = bcast[1];
+  const float l = m + __logf(s);
+  if (tid == 0) {
+    lse[row] = l;
+    row_loss[row] = (tg < 0) ? 0.f : l - __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(ce_smem)[tg]);
+  }
+  // ---- pass 3: softmax - onehot (0 for ignored rows and for the padding columns V..ld-1), over the logits
+  const float lneg = -l * kLog2e;
+  const bool liverow = tg >= 0;
+  const int tvec = liverow ? static_cast<int>(tg >> 3) : -1, tk = static_cast<int>(tg & 7);
+  uint4* gout = reinterpret_cast<uint4*>(grow);
+  for (int i = tid; i < nvec; i += kCeFusedThreads) {
+    float o[8];
+    if (!liverow) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+    } else {
+      const uint4 u = srow[i];
+      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      o[0] = ex2(fmaf(a.x, kLog2e, lneg)); o[1] = ex2(fmaf(a.y, kLog2e, lneg));
+      o[2] = ex2(fmaf(b.x, kLog2e, lneg)); o[3] = ex2(fmaf(b.y, kLog2e, lneg));
+      o[4] = ex2(fmaf(c.x, kLog2e, lneg)); o[5] = ex2(fmaf(c.y, kLog2e, lneg));
+      o[6] = ex2(fmaf(d.x, kLog2e, lneg)); o[7] = ex2(fmaf(d.y, kLog2e, lneg));
+      if (i >= nfull) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (i * 8 + k >= V) o[k] = 0.f;
+      }
+      if (i == tvec) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (k == tk) o[k] -= 1.f;
+      }
+    }
+    st_stream(gout + i, make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7])));
+  }
+}
+
 // =============================================================================================
 // K12 grad norm + clip coefficient
 // =============================================================================================
@@ -1017,6 +1155,28 @@ int nsb_cross_entropy_bwd(void* logits, int dtype, const int64_t* targets, const
 #undef CE_BWD
   count_launch();
   return check_launch("cross_entropy_bwd");
+}
+
+int nsb_cross_entropy_fwd_bwd(void* logits, int dtype, const int64_t* targets, float* lse,
+                              float* row_loss, float* stats, int M, int V, int ld, nsb_stream_t stream) {
+  NSB_REQUIRE(dtype == NSB_BF16, "cross_entropy_fwd_bwd: bf16 logits only (dtype %d); use the separate passes", dtype);
+  NSB_REQUIRE(ld >= V && V >= 1, "cross_entropy_fwd_bwd: ld %d < V %d", ld, V);
+  NSB_REQUIRE(M >= 1, "cross_entropy_fwd_bwd: empty batch");
+  NSB_REQUIRE(ld % 8 == 0 && aligned16(logits), "cross_entropy_fwd_bwd: rows must be 16-byte aligned (ld %d)", ld);
+  const size_t smem = static_cast<size_t>(ld) * 2;
+  NSB_REQUIRE(smem <= 232448 - 1024, "cross_entropy_fwd_bwd: a row of %d logits does not fit in shared memory; "
+              "use the separate passes", ld);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(cross_entropy_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024);
+    NSB_REQUIRE(e == cudaSuccess, "cross_entropy_fwd_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    attr_set = true;
+  }
+  launch_pdl(cross_entropy_fused_kernel, dim3(M), dim3(kCeFusedThreads), smem, cs(stream),
+             static_cast<__nv_bfloat16*>(logits), targets, lse, row_loss, V, ld);
+  launch_pdl(cross_entropy_reduce_kernel, dim3(1), dim3(1024), 0, cs(stream), row_loss, targets, stats, M);
+  count_launch(2);
+  return check_launch("cross_entropy_fwd_bwd");
 }
 
 static inline int norm_grid(size_t n) { return static_cast<int>(grid_for(n / 4, 256 * 8, 8 * 160)); }

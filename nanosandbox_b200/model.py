@@ -141,7 +141,7 @@ class _FusedStep(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, anchor, model, idx, targets):
-        logits, loss = model._engine_forward(idx, targets)
+        logits, loss = model._engine_forward(idx, targets, for_backward=True)
         ctx.model = model
         ctx.mark_non_differentiable(logits)
         ctx.set_materialize_grads(False)  # no [B,T,V] zeros tensor for the unused logits gradient
@@ -184,6 +184,10 @@ class GPT(nn.Module):
         # bf16 path: GELU as its own memory-bound kernels (faster on B200 than the fused GEMM epilogues,
         # whose eight epilogue warps cannot hide the erf math behind a K = 768 mainloop)
         self.split_gelu = True
+        # Training forward (bf16): the loss kernel also leaves softmax - onehot in the logits buffer (one
+        # pass over the 1.2 GB of logits instead of two), so the `logits` returned next to the loss then
+        # hold that gradient, not the logits.  Set to False if you read the logits of a training forward.
+        self.fuse_loss_backward = True
         self._micro_step_has_grads = False
 
     # ------------------------------------------------------------------ nanoGPT surface
@@ -368,7 +372,7 @@ class GPT(nn.Module):
             self._acts[key] = a
         return a
 
-    def _engine_forward(self, idx, targets):
+    def _engine_forward(self, idx, targets, for_backward=False):
         cfg = self.config
         arena = self.arena()
         if not idx.is_cuda:
@@ -420,7 +424,11 @@ class GPT(nn.Module):
         a.targets = targets
         ops.gemm(M, V, C, a.lnf, C, True, wte, C, True, a.logits, a.ldv, EPI_STORE, stream=st)
         a.stats = torch.empty(2, dtype=torch.float32, device=idx.device)
-        ops.cross_entropy_fwd(a.logits, targets, a.ce_lse, a.ce_row, a.stats, V, st)
+        a.ce_fused = bool(for_backward and self.fuse_loss_backward and ops.cross_entropy_fused_ok(a.logits))
+        if a.ce_fused:
+            ops.cross_entropy_fwd_bwd(a.logits, targets, a.ce_lse, a.ce_row, a.stats, V, st)
+        else:
+            ops.cross_entropy_fwd(a.logits, targets, a.ce_lse, a.ce_row, a.stats, V, st)
         self._last_acts = a
         # NOTE: the logits buffer is reused: backward() turns it into dlogits in place and the next
         # forward overwrites it.  Clone it if you need the values later.
@@ -451,9 +459,16 @@ class GPT(nn.Module):
                 ops.colsum(dy[:, :n_out], G(name + ".bias"), True, st)
 
         # ---- head: dlogits in place, tied lm_head wgrad + dgrad, ln_f
-        ops.cross_entropy_bwd(a.logits, a.targets, a.ce_lse, a.stats, gs, V, st)
-        wgrad(a.logits, a.ldv, a.lnf, C, "transformer.wte", V, C)
-        ops.gemm(M, C, V, a.logits, a.ldv, True, W("transformer.wte.weight"), C, False, a.dln, C, EPI_STORE, stream=st)
+        if a.ce_fused:
+            # the logits buffer already holds softmax - onehot; gscale / n_valid rides on the two GEMMs
+            head_alpha = (gs.reshape(()) / a.stats[1]).reshape(1)
+        else:
+            ops.cross_entropy_bwd(a.logits, a.targets, a.ce_lse, a.stats, gs, V, st)
+            head_alpha = None
+        ops.gemm(V, C, M, a.logits, a.ldv, False, a.lnf, C, False, G("transformer.wte.weight"), C, EPI_ACCUM,
+                 alpha=head_alpha, accumulate=True, stream=st)
+        ops.gemm(M, C, V, a.logits, a.ldv, True, W("transformer.wte.weight"), C, False, a.dln, C, EPI_STORE,
+                 alpha=head_alpha, stream=st)
         cur = 0
         ops.layernorm_bwd(a.dln, a.x[L], P("transformer.ln_f.weight"), a.statf[0], a.statf[1], None,
                           a.dres[cur], a.dres_lowp, G("transformer.ln_f.weight"),

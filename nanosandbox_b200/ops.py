@@ -80,6 +80,21 @@ def cross_entropy_fwd(logits, targets, lse, row_loss, stats, V, stream=None):
                                             stream or stream_handle()), "cross_entropy_fwd")
 
 
+def cross_entropy_fwd_bwd(logits, targets, lse, row_loss, stats, V, stream=None):
+    """Loss statistics and, in place, the UNSCALED gradient softmax - onehot (bf16 logits only)."""
+    _require_cuda(logits, "logits")
+    M, ld = logits.shape[0], logits.stride(0)
+    check(_lib.load().nsb_cross_entropy_fwd_bwd(logits.data_ptr(), dtype_code(logits), targets.data_ptr(),
+                                                lse.data_ptr(), row_loss.data_ptr(), stats.data_ptr(), M, V, ld,
+                                                stream or stream_handle()), "cross_entropy_fwd_bwd")
+
+
+def cross_entropy_fused_ok(logits) -> bool:
+    """True if nsb_cross_entropy_fwd_bwd accepts this logits buffer (bf16, aligned rows that fit in smem)."""
+    ld = logits.stride(0)
+    return logits.dtype == torch.bfloat16 and ld % 8 == 0 and ld * 2 <= 232448 - 1024 and logits.data_ptr() % 16 == 0
+
+
 def cross_entropy_bwd(logits, targets, lse, stats, gscale, V, stream=None):
     M, ld = logits.shape[0], logits.stride(0)
     check(_lib.load().nsb_cross_entropy_bwd(logits.data_ptr(), dtype_code(logits), targets.data_ptr(),

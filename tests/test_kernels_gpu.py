@@ -122,6 +122,50 @@ def test_cross_entropy(V, ld, dt):
     assert (store[5] == 0).all() and (store[100] == 0).all()
 
 
+@pytest.mark.parametrize("V,ld", [(1000, 1000), (50257, 50304), (65, 72), (50304, 50304)])
+def test_cross_entropy_fused_fwd_bwd(V, ld):
+    """One-pass loss + unscaled gradient against torch, and against the two separate passes."""
+    torch.manual_seed(12)
+    M = 131
+    store = (torch.randn(M, ld, device=DEV) * 3).to(torch.bfloat16)
+    keep = store.clone()
+    targets = torch.randint(0, V, (M,), device=DEV)
+    targets[7] = -1
+    targets[M - 1] = V - 1
+    lse, rl, stats = torch.empty(M, device=DEV), torch.empty(M, device=DEV), torch.empty(2, device=DEV)
+    assert ops.cross_entropy_fused_ok(store)
+    ops.cross_entropy_fwd_bwd(store, targets, lse, rl, stats, V)
+    lr = keep[:, :V].float().clone().requires_grad_(True)
+    ref = F.cross_entropy(lr, targets, ignore_index=-1)
+    assert abs(stats[0].item() - ref.item()) < 1e-4 * max(1.0, abs(ref.item())), (stats, ref)
+    assert stats[1].item() == M - 1
+    assert_close(lse, torch.logsumexp(keep[:, :V].float(), -1), 1e-5, "lse")
+    ref.backward()
+    assert_close(store[:, :V].float() / (M - 1), lr.grad, 6e-3, "dlogits (unscaled / n_valid)")
+    if ld > V:
+        assert (store[:, V:] == 0).all()
+    assert (store[7] == 0).all()
+    # the separate passes with gscale = n_valid produce the same unscaled gradient up to one bf16 rounding
+    two = keep.clone()
+    lse2, rl2, st2 = torch.empty(M, device=DEV), torch.empty(M, device=DEV), torch.empty(2, device=DEV)
+    ops.cross_entropy_fwd(two, targets, lse2, rl2, st2, V)
+    ops.cross_entropy_bwd(two, targets, lse2, st2, torch.tensor([float(M - 1)], device=DEV), V)
+    assert_close(lse, lse2, 1e-5, "lse vs two-pass")
+    assert_close(rl, rl2, 1e-5, "row loss vs two-pass")
+    assert_close(store.float(), two.float(), 1e-2, "dlogits vs two-pass")
+
+
+def test_cross_entropy_fused_rejects_what_it_cannot_do():
+    M, V = 4, 100
+    lse, rl, stats = torch.empty(M, device=DEV), torch.empty(M, device=DEV), torch.empty(2, device=DEV)
+    tg = torch.zeros(M, dtype=torch.int64, device=DEV)
+    with pytest.raises(_lib.NsbError):
+        ops.cross_entropy_fwd_bwd(torch.zeros(M, V, device=DEV), tg, lse, rl, stats, V)            # fp32
+    with pytest.raises(_lib.NsbError):
+        ops.cross_entropy_fwd_bwd(torch.zeros(M, 200000, device=DEV, dtype=torch.bfloat16), tg, lse, rl, stats, V)
+    assert not ops.cross_entropy_fused_ok(torch.zeros(M, 100, device=DEV, dtype=torch.bfloat16))  # ld % 8 != 0
+
+
 def test_grad_norm_and_adamw_match_torch():
     torch.manual_seed(3)
     n = 1024 * 37

@@ -21,6 +21,9 @@ print("compute warp per iteration: [top, sdp_full seen, P/dS in regs, dq_full(it
 for it in range(8):
     r = [x - t0 for x in d[8 * it:8 * it + 6]]
     print(it, r, "wait_sdp", r[1] - r[0], "compute", r[2] - r[1], "wait_dq", r[3] - r[2], "store", r[4] - r[3], "writeback", r[5] - r[4])
+print("inside the probabilities step (rel. sdp_full seen): [tmem 0 landed, math 0 done, tmem 1 landed, math 1 done]")
+for it in range(8):
+    print(it, [x - d[8 * it + 1] for x in d[256 + 4 * it:256 + 4 * it + 4]])
 print("mma warp per iteration: [top, pds_full seen, dV/dK issued, dq_free seen]")
 for it in range(8):
     print(it, [x - t0 for x in d[512 + 4 * it:512 + 4 * it + 4]])
