@@ -509,6 +509,7 @@ __global__ void __launch_bounds__(448, 1)
       // writing P^T / dS^T to shared memory at that point)
       if (it + 1 < nit) {
         ptx::mbar_wait(sdp_free, it & 1);
+        if (recm) dbg[512 + 4 * it + 2] = clock64();          // S/dP of this block read out
         ptx::mbar_wait(&qdo_full[(it + 1) % QS], ((it + 1) / QS) & 1);
         ptx::tc_fence_after();
         issue_sdp(it + 1);
@@ -531,7 +532,6 @@ __global__ void __launch_bounds__(448, 1)
         }
       }
       __syncwarp();
-      if (recm) dbg[512 + 4 * it + 2] = clock64();
       if (it > 0) { ptx::mbar_wait(dq_free, (it - 1) & 1); ptx::tc_fence_after(); }
       if (recm) dbg[512 + 4 * it + 3] = clock64();
       if (ptx::elect_one()) {

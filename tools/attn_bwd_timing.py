@@ -24,6 +24,6 @@ for it in range(8):
 print("inside the probabilities step (rel. sdp_full seen): [tmem 0 landed, math 0 done, tmem 1 landed, math 1 done]")
 for it in range(8):
     print(it, [x - d[8 * it + 1] for x in d[256 + 4 * it:256 + 4 * it + 4]])
-print("mma warp per iteration: [top, pds_full seen, dV/dK issued, dq_free seen]")
+print("mma warp per iteration: [top, pds_full seen, sdp_free seen (before S/dP of the next block is issued), dq_free seen]")
 for it in range(8):
     print(it, [x - t0 for x in d[512 + 4 * it:512 + 4 * it + 4]])
