@@ -548,6 +548,7 @@ __global__ void __launch_bounds__(128)
 namespace nsb {
 int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, int H, cudaStream_t stream);
 void attention_tc_set_debug_buffer(long long* p);
+void attention_tc_set_dq_direct(int on);
 int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
                             float* delta, float* dq_acc, int B, int T, int H, cudaStream_t stream);
 }
@@ -557,7 +558,12 @@ static int g_attn_force_simt = 0;   // 1: exact SIMT kernels, 2: mma.sync flash 
 
 extern "C" {
 
-void nsb_attention_debug_config(int force_simt) { g_attn_force_simt = force_simt; }
+// 0: tensor-core kernels, 1: SIMT, 2: mma.sync; 3 / 4: tensor-core backward with dQ staged through shared
+// memory + TMA reduce-add (the default) / reduced straight from registers
+void nsb_attention_debug_config(int force_simt) {
+  if (force_simt == 3 || force_simt == 4) { attention_tc_set_dq_direct(force_simt == 4); g_attn_force_simt = 0; return; }
+  g_attn_force_simt = force_simt;
+}
 // device buffer (>= 1024 int64) receiving phase timestamps of one CTA of the tcgen05 kernels; NULL = off
 void nsb_attention_debug_timing(void* device_buffer) { attention_tc_set_debug_buffer(static_cast<long long*>(device_buffer)); }
 
