@@ -18,6 +18,7 @@ parity mode).
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 
 import torch
@@ -188,6 +189,10 @@ class GPT(nn.Module):
         # pass over the 1.2 GB of logits instead of two), so the `logits` returned next to the loss then
         # hold that gradient, not the logits.  Set to False if you read the logits of a training forward.
         self.fuse_loss_backward = True
+        # Weight-gradient GEMMs run on a side stream: nothing in the backward chain depends on them, so
+        # their CTAs fill the SMs that the chain's kernels leave idle in their ramp-up and tail.
+        self.overlap_wgrad = os.environ.get("NSB_OVERLAP_WGRAD", "1") != "0"
+        self._wgrad_stream = None
         self._micro_step_has_grads = False
 
     # ------------------------------------------------------------------ nanoGPT surface
@@ -451,12 +456,36 @@ class GPT(nn.Module):
         sync = self._grad_sync
         act = (lambda t32, tl: tl) if lowp else (lambda t32, tl: t32)
 
-        def wgrad(dy, dy_ld, x, x_ld, name, n_out, n_in):
+        main = torch.cuda.current_stream()
+        side = None
+        if self.overlap_wgrad:
+            if self._wgrad_stream is None or self._wgrad_stream.device != main.device:
+                self._wgrad_stream = torch.cuda.Stream(device=main.device)
+            side = self._wgrad_stream
+        st_w = side.cuda_stream if side is not None else st
+        pending = {}     # buffer name -> event: the side stream has finished reading that dY buffer
+
+        def wgrad(dy, dy_ld, x, x_ld, name, n_out, n_in, alpha=None, reads=None):
             # dW[n_out, n_in] += dy^T x ; both operands read "transposed" in place (MN-major)
+            if side is not None:
+                side.wait_event(main.record_event())          # dy is complete on the main stream
             ops.gemm(n_out, n_in, M, dy, dy_ld, False, x, x_ld, False, G(name + ".weight"), n_in, EPI_ACCUM,
-                     accumulate=True, stream=st)
+                     alpha=alpha, accumulate=True, stream=st_w)
             if has_bias and (name + ".bias") in arena.slots:
-                ops.colsum(dy[:, :n_out], G(name + ".bias"), True, st)
+                ops.colsum(dy[:, :n_out], G(name + ".bias"), True, st_w)
+            if side is not None and reads is not None:
+                pending[reads] = side.record_event()
+
+        def before_overwrite(buf):
+            # the main stream is about to rewrite a dY buffer a weight-gradient GEMM may still be reading
+            ev = pending.pop(buf, None)
+            if ev is not None:
+                main.wait_event(ev)
+
+        def join_side():
+            if side is not None:
+                main.wait_event(side.record_event())
+                pending.clear()
 
         # ---- head: dlogits in place, tied lm_head wgrad + dgrad, ln_f
         if a.ce_fused:
@@ -465,8 +494,8 @@ class GPT(nn.Module):
         else:
             ops.cross_entropy_bwd(a.logits, a.targets, a.ce_lse, a.stats, gs, V, st)
             head_alpha = None
-        ops.gemm(V, C, M, a.logits, a.ldv, False, a.lnf, C, False, G("transformer.wte.weight"), C, EPI_ACCUM,
-                 alpha=head_alpha, accumulate=True, stream=st)
+        a.head_alpha = head_alpha   # stays alive until the side stream has used it
+        wgrad(a.logits, a.ldv, a.lnf, C, "transformer.wte", V, C, alpha=head_alpha)
         ops.gemm(M, C, V, a.logits, a.ldv, True, W("transformer.wte.weight"), C, False, a.dln, C, EPI_STORE,
                  alpha=head_alpha, stream=st)
         cur = 0
@@ -478,7 +507,8 @@ class GPT(nn.Module):
             s = a.stat[l]
             dres, dres_a = a.dres[cur], act(a.dres[cur], a.dres_lowp)
             # MLP
-            wgrad(dres_a, C, a.fca[l], 4 * C, pre + "mlp.c_proj", C, 4 * C)
+            wgrad(dres_a, C, a.fca[l], 4 * C, pre + "mlp.c_proj", C, 4 * C, reads="dres")
+            before_overwrite("dh")
             if lowp and self.split_gelu:
                 ops.gemm(M, 4 * C, C, dres_a, C, True, W(pre + "mlp.c_proj.weight"), 4 * C, False, a.dh, 4 * C,
                          EPI_STORE, stream=st)
@@ -486,25 +516,31 @@ class GPT(nn.Module):
             else:
                 ops.gemm(M, 4 * C, C, dres_a, C, True, W(pre + "mlp.c_proj.weight"), 4 * C, False, a.dh, 4 * C,
                          EPI_DGELU, aux=a.fch[l], stream=st)
-            wgrad(a.dh, 4 * C, a.ln2[l], C, pre + "mlp.c_fc", 4 * C, C)
+            wgrad(a.dh, 4 * C, a.ln2[l], C, pre + "mlp.c_fc", 4 * C, C, reads="dh")
             ops.gemm(M, C, 4 * C, a.dh, 4 * C, True, W(pre + "mlp.c_fc.weight"), C, False, a.dln, C, EPI_STORE, stream=st)
+            before_overwrite("dres")
             ops.layernorm_bwd(a.dln, a.xmid[l], P(pre + "ln_2.weight"), s[2], s[3], dres, a.dres[cur ^ 1],
                               a.dres_lowp, G(pre + "ln_2.weight"), G(pre + "ln_2.bias") if has_bias else None,
                               True, a.ln_scratch, st)
             cur ^= 1
             dres, dres_a = a.dres[cur], act(a.dres[cur], a.dres_lowp)
             # attention
-            wgrad(dres_a, C, a.att[l], C, pre + "attn.c_proj", C, C)
+            wgrad(dres_a, C, a.att[l], C, pre + "attn.c_proj", C, C, reads="dres")
             ops.gemm(M, C, C, dres_a, C, True, W(pre + "attn.c_proj.weight"), C, False, a.datt, C, EPI_STORE, stream=st)
+            before_overwrite("dqkv")
             ops.attention_bwd(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D, a.dq_acc, st)
-            wgrad(a.dqkv, 3 * C, a.ln1[l], C, pre + "attn.c_attn", 3 * C, C)
+            wgrad(a.dqkv, 3 * C, a.ln1[l], C, pre + "attn.c_attn", 3 * C, C, reads="dqkv")
             ops.gemm(M, C, 3 * C, a.dqkv, 3 * C, True, W(pre + "attn.c_attn.weight"), C, False, a.dln, C, EPI_STORE, stream=st)
+            before_overwrite("dres")
             ops.layernorm_bwd(a.dln, a.x[l], P(pre + "ln_1.weight"), s[0], s[1], dres, a.dres[cur ^ 1],
                               a.dres_lowp, G(pre + "ln_1.weight"), G(pre + "ln_1.bias") if has_bias else None,
                               True, a.ln_scratch, st)
             cur ^= 1
+            if sync is not None and getattr(sync, "require_backward_grad_sync", True):
+                join_side()          # the bucket's weight gradients come from the side stream
             if sync is not None:
                 sync.bucket_ready(i)
+        join_side()                  # wte: lm_head weight gradient before the embedding scatter; also the final join
         ops.embedding_bwd(a.idx, a.dres[cur], G("transformer.wte.weight"), G("transformer.wpe.weight"), True, st)
         if sync is not None:
             sync.bucket_ready(L)
