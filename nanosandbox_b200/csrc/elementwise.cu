@@ -877,7 +877,8 @@ __device__ __forceinline__ uint4 gelu8(const uint4 u) {
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     const float2 x = unpack_bf16x2(w[k]);
-    o[k] = pack_bf16x2(gelu_fast(x.x), gelu_fast(x.y));
+    const float2 y = gelu_fast2(x.x, x.y);
+    o[k] = pack_bf16x2(y.x, y.y);
   }
   return make_uint4(o[0], o[1], o[2], o[3]);
 }
@@ -887,7 +888,8 @@ __device__ __forceinline__ uint4 dgelu8(const uint4 g, const uint4 u) {
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     const float2 x = unpack_bf16x2(hw[k]), d = unpack_bf16x2(gw[k]);
-    o[k] = pack_bf16x2(d.x * gelu_fast_grad(x.x), d.y * gelu_fast_grad(x.y));
+    const float2 y = gelu_fast_grad_mul2(x.x, x.y, d.x, d.y);
+    o[k] = pack_bf16x2(y.x, y.y);
   }
   return make_uint4(o[0], o[1], o[2], o[3]);
 }
