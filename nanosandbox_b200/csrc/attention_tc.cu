@@ -58,14 +58,30 @@ __device__ __forceinline__ float softmax_pass(uint32_t s_addr, uint8_t* sP, int 
     float* cur = (c & 1) ? vb : va;
     float* nxt = (c & 1) ? va : vb;
     if (c < 3) ptx::tmem_ld_32x32_async(s_addr + (c + 1) * 32, nxt);
+    if (DIAG) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      if (DIAG) { if (c * 32 + i <= lim) mx = fmaxf(mx, cur[i]); }
-      else mx = fmaxf(mx, cur[i]);
-      float p = ex2(fmaf(cur[i], scale_log2, -m));
-      if (DIAG) { if (c * 32 + i > lim) p = 0.f; }
-      cur[i] = p;
-      if (i & 1) s1 += p; else s0 += p;
+      for (int i = 0; i < 32; ++i) {
+        if (c * 32 + i <= lim) mx = fmaxf(mx, cur[i]);
+        float p = ex2(fmaf(cur[i], scale_log2, -m));
+        if (c * 32 + i > lim) p = 0.f;
+        cur[i] = p;
+        if (i & 1) s1 += p; else s0 += p;
+      }
+    } else {
+      // full block: two columns per step on the packed fp32 pipe (same operations and summation order
+      // as the scalar loop above: even columns into s0, odd ones into s1) and a 3-input max
+      const f32x2 sc2 = pack2(scale_log2, scale_log2), nm2 = pack2(-m, -m);
+      f32x2 acc = pack2(s0, s1);
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        mx = max3(mx, cur[i], cur[i + 1]);
+        float a0, a1;
+        unpack2(fma2(pack2(cur[i], cur[i + 1]), sc2, nm2), a0, a1);
+        cur[i] = ex2(a0);
+        cur[i + 1] = ex2(a1);
+        acc = add2(acc, pack2(cur[i], cur[i + 1]));
+      }
+      unpack2(acc, s0, s1);
     }
     uint8_t* atom = sP + (c >> 1) * TILE;
     // the previous block's P V may still be reading this tile: wait right before the first store
@@ -380,21 +396,27 @@ __device__ __forceinline__ void bwd_probs(uint32_t taddr, const float* lse2, con
     ptx::tmem_wait_ld32(sv);
     ptx::tmem_wait_ld32(dv);
     if (trace != nullptr) trace[2 * c] = clock64() + (__float_as_int(sv[0]) & 0) + (__float_as_int(dv[31]) & 0);
+    // the per-query statistics are stored negated (-lse*log2e, -delta), so a pair of columns costs one
+    // packed fma, two exp2, one packed add and one packed multiply
+    const f32x2 sc2 = pack2(scale_log2, scale_log2);
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
       const float4 l4 = *reinterpret_cast<const float4*>(lse2 + c * 32 + i);
       const float4 d4 = *reinterpret_cast<const float4*>(dlt + c * 32 + i);
-      const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
+      const float nl[4] = {l4.x, l4.y, l4.z, l4.w}, nd[4] = {d4.x, d4.y, d4.z, d4.w};
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        float p = ex2(fmaf(sv[i + e], scale_log2, -ls[e]));
+      for (int e = 0; e < 4; e += 2) {
+        float a0, a1;
+        unpack2(fma2(pack2(sv[i + e], sv[i + e + 1]), sc2, pack2(nl[e], nl[e + 1])), a0, a1);
+        float p0 = ex2(a0), p1 = ex2(a1);
         if (MASK) {
           const int col = col0 + c * 32 + i + e;               // query column within the block
-          const bool ok = (col < qlim) && (!diag || col >= row);
-          p = ok ? p : 0.f;
+          p0 = ((col < qlim) && (!diag || col >= row)) ? p0 : 0.f;
+          p1 = ((col + 1 < qlim) && (!diag || col + 1 >= row)) ? p1 : 0.f;
         }
-        sv[i + e] = p;
-        dv[i + e] = p * (dv[i + e] - ds[e]);
+        sv[i + e] = p0;
+        sv[i + e + 1] = p1;
+        unpack2(mul2(pack2(p0, p1), add2(pack2(dv[i + e], dv[i + e + 1]), pack2(nd[e], nd[e + 1]))), dv[i + e], dv[i + e + 1]);
       }
     }
 #pragma unroll
@@ -609,7 +631,7 @@ __global__ void __launch_bounds__(448, 1)
     auto load_stat = [&](int it) -> float {
       const int qg = (jb + it) * BQ + (ct & 127);
       if (qg >= Tn) return 0.f;
-      return ct < 128 ? lse_g[qg] * 1.4426950408889634f : del_g[qg];
+      return ct < 128 ? -lse_g[qg] * 1.4426950408889634f : -del_g[qg];   // negated: see bwd_probs
     };
     float st_next = load_stat(0);
     const bool rec = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;

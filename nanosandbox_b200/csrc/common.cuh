@@ -117,6 +117,7 @@ __device__ __forceinline__ void unpack2(f32x2 x, float& a, float& b) { asm("mov.
 __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
 __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
 __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ float max3(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
 // Phi(x0), Phi(x1) and the two unscaled densities exp(-x^2/2)
 __device__ __forceinline__ void gelu_fast_parts2(float x0, float x1, float& cdf0, float& cdf1, f32x2& pdf_unscaled) {
   const float t0 = mufu_rcp(fmaf(0.3275911f * 0.70710678118654752440f, fabsf(x0), 1.0f));

@@ -672,18 +672,30 @@ __global__ void __launch_bounds__(kCeFusedThreads, 2)
   auto ex2 = [](float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; };
   // ---- pass 2: sum of exp(x - max)
   const float mneg = -m * kLog2e;
+  const f32x2 l2e2 = pack2(kLog2e, kLog2e), mneg2 = pack2(mneg, mneg);
+  f32x2 s2 = pack2(0.f, 0.f);
   float s = 0.f;
   for (int i = tid; i < nvec; i += kCeFusedThreads) {
     const uint4 u = srow[i];
     if (i < nfull) {
-      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-      s += (ex2(fmaf(a.x, kLog2e, mneg)) + ex2(fmaf(a.y, kLog2e, mneg))) + (ex2(fmaf(b.x, kLog2e, mneg)) + ex2(fmaf(b.y, kLog2e, mneg))) +
-           (ex2(fmaf(c.x, kLog2e, mneg)) + ex2(fmaf(c.y, kLog2e, mneg))) + (ex2(fmaf(d.x, kLog2e, mneg)) + ex2(fmaf(d.y, kLog2e, mneg)));
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {                 // packed fp32: one fma and one add per pair of logits
+        const float2 x = unpack_bf16x2(w[k]);
+        float a0, a1;
+        unpack2(fma2(pack2(x.x, x.y), l2e2, mneg2), a0, a1);
+        s2 = add2(s2, pack2(ex2(a0), ex2(a1)));
+      }
     } else {
       const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&u);
       for (int k = 0; k < 8; ++k)
         if (i * 8 + k < V) s += ex2(fmaf(__bfloat162float(e[k]), kLog2e, mneg));
     }
+  }
+  {
+    float e0, e1;
+    unpack2(s2, e0, e1);
+    s += e0 + e1;
   }
   s = warp_sum(s);
   if (lane == 0) red[warp] = s;
@@ -702,6 +714,7 @@ __global__ void __launch_bounds__(kCeFusedThreads, 2)
   }
   // ---- pass 3: softmax - onehot (0 for ignored rows and for the padding columns V..ld-1), over the logits
   const float lneg = -l * kLog2e;
+  const f32x2 lneg2 = pack2(lneg, lneg);
   const bool liverow = tg >= 0;
   const int tvec = liverow ? static_cast<int>(tg >> 3) : -1, tk = static_cast<int>(tg & 7);
   uint4* gout = reinterpret_cast<uint4*>(grow);
@@ -712,11 +725,15 @@ __global__ void __launch_bounds__(kCeFusedThreads, 2)
       for (int k = 0; k < 8; ++k) o[k] = 0.f;
     } else {
       const uint4 u = srow[i];
-      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-      o[0] = ex2(fmaf(a.x, kLog2e, lneg)); o[1] = ex2(fmaf(a.y, kLog2e, lneg));
-      o[2] = ex2(fmaf(b.x, kLog2e, lneg)); o[3] = ex2(fmaf(b.y, kLog2e, lneg));
-      o[4] = ex2(fmaf(c.x, kLog2e, lneg)); o[5] = ex2(fmaf(c.y, kLog2e, lneg));
-      o[6] = ex2(fmaf(d.x, kLog2e, lneg)); o[7] = ex2(fmaf(d.y, kLog2e, lneg));
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 x = unpack_bf16x2(w[k]);
+        float a0, a1;
+        unpack2(fma2(pack2(x.x, x.y), l2e2, lneg2), a0, a1);
+        o[2 * k] = ex2(a0);
+        o[2 * k + 1] = ex2(a1);
+      }
       if (i >= nfull) {
 #pragma unroll
         for (int k = 0; k < 8; ++k)
