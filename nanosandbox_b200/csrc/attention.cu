@@ -549,6 +549,7 @@ namespace nsb {
 int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, int H, cudaStream_t stream);
 void attention_tc_set_debug_buffer(long long* p);
 void attention_tc_set_dq_direct(int on);
+void attention_tc_set_kv_tmem(int on);
 int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
                             float* delta, float* dq_acc, int B, int T, int H, cudaStream_t stream);
 }
@@ -562,6 +563,8 @@ extern "C" {
 // memory + TMA reduce-add (the default) / reduced straight from registers
 void nsb_attention_debug_config(int force_simt) {
   if (force_simt == 3 || force_simt == 4) { attention_tc_set_dq_direct(force_simt == 4); g_attn_force_simt = 0; return; }
+  // 5 / 6: tensor-core backward with K, V read from shared memory (the default) / from tensor memory
+  if (force_simt == 5 || force_simt == 6) { attention_tc_set_kv_tmem(force_simt == 6); g_attn_force_simt = 0; return; }
   g_attn_force_simt = force_simt;
 }
 // device buffer (>= 1024 int64) receiving phase timestamps of one CTA of the tcgen05 kernels; NULL = off

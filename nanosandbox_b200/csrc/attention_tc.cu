@@ -328,6 +328,8 @@ static long long* g_attn_dbg = nullptr;
 void attention_tc_set_debug_buffer(long long* p) { g_attn_dbg = p; }
 static int g_attn_dq_direct = 0;   // 1: dQ leaves by vector reductions from registers (measured slower: 184 vs 156 us); 0: staged TMA reduce-add
 void attention_tc_set_dq_direct(int on) { g_attn_dq_direct = on; }
+static int g_attn_kv_tmem = 0;     // 1: K / V as tensor-memory A operands of the S^T / dP^T MMAs (bit-identical, measured no faster: the compute warps are the critical path)
+void attention_tc_set_kv_tmem(int on) { g_attn_kv_tmem = on; }
 
 int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, int H, cudaStream_t stream) {
   using namespace fatc;
@@ -379,6 +381,7 @@ constexpr int OFF_BAR = OFF_STAT + 2 * 2 * 128 * 4;
 constexpr int SMEM_BYTES = OFF_BAR + 256;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
+constexpr uint32_t C_KA = 448, C_VA = 480;   // K and V rows as tensor-memory A operands (bf16 pairs, 32 columns each)
 }  // namespace fabw
 
 // 64 query columns of one key row: P^T = exp2(S^T*scale - lse[q]) and dS^T = P^T (dP^T - delta[q]),
@@ -432,7 +435,7 @@ __global__ void __launch_bounds__(448, 1)
     attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_dy,
                        const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse,
                        const float* __restrict__ delta, __nv_bfloat16* __restrict__ dqkv, int Tn, int H,
-                       float scale, float scale_log2, float* __restrict__ dq_acc, int dq_direct, long long* dbg) {
+                       float scale, float scale_log2, float* __restrict__ dq_acc, int dq_direct, int kv_in_tmem, long long* dbg) {
   using namespace fabw;
   using fatc::ex2;
   using fatc::sw128;
@@ -447,6 +450,7 @@ __global__ void __launch_bounds__(448, 1)
   uint64_t* dq_free = bars + 10;     // dQ columns read back                           count 4
   uint64_t* dkv_full = bars + 11;
   uint64_t* sdp_free = bars + 12;    // S^T / dP^T read into registers (TMEM columns reusable)  count 8
+  uint64_t* kv_tmem = bars + 13;     // K / V rows copied into tensor memory             count 8
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
   float* stat = reinterpret_cast<float*>(smem + OFF_STAT);
 
@@ -470,6 +474,7 @@ __global__ void __launch_bounds__(448, 1)
     ptx::mbar_init(dq_full, 1);
     ptx::mbar_init(dq_free, 4);
     ptx::mbar_init(dkv_full, 1);
+    ptx::mbar_init(kv_tmem, 8);
     ptx::mbar_init(sdp_free, 8);
     ptx::fence_mbar_init();
   }
@@ -512,16 +517,21 @@ __global__ void __launch_bounds__(448, 1)
       const uint64_t do_k = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, 16, 1024);
       if (ptx::elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          ptx::umma_bf16(tmem + C_S, dK_ + static_cast<uint64_t>(2 * k), q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+        for (int k = 0; k < 4; ++k) {
+          if (kv_in_tmem) ptx::umma_bf16_ts(tmem + C_S, tmem + C_KA + 8 * k, q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+          else ptx::umma_bf16(tmem + C_S, dK_ + static_cast<uint64_t>(2 * k), q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+        }
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          ptx::umma_bf16(tmem + C_DP, dV_ + static_cast<uint64_t>(2 * k), do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+        for (int k = 0; k < 4; ++k) {
+          if (kv_in_tmem) ptx::umma_bf16_ts(tmem + C_DP, tmem + C_VA + 8 * k, do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+          else ptx::umma_bf16(tmem + C_DP, dV_ + static_cast<uint64_t>(2 * k), do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+        }
         ptx::umma_commit(sdp_full);
       }
       __syncwarp();
     };
     ptx::mbar_wait(kv_full, 0);
+    if (kv_in_tmem) ptx::mbar_wait(kv_tmem, 0);
     ptx::mbar_wait(&qdo_full[0], 0);
     ptx::tc_fence_after();
     issue_sdp(0);
@@ -634,6 +644,22 @@ __global__ void __launch_bounds__(448, 1)
       return ct < 128 ? -lse_g[qg] * 1.4426950408889634f : -del_g[qg];   // negated: see bwd_probs
     };
     float st_next = load_stat(0);
+    if (kv_in_tmem) {
+      // this thread's key row of K (group 0) or V (group 1): swizzled smem -> registers -> tensor memory,
+      // where the S^T / dP^T MMAs read it as their A operand for the whole loop
+      ptx::mbar_wait(kv_full, 0);
+      float rowv[32];
+      const uint8_t* src = smem + (wg == 0 ? OFF_K : OFF_V);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 v4 = *reinterpret_cast<const float4*>(src + sw128(row, i));
+        rowv[4 * i] = v4.x; rowv[4 * i + 1] = v4.y; rowv[4 * i + 2] = v4.z; rowv[4 * i + 3] = v4.w;
+      }
+      ptx::tmem_st_32x32(tmem + lane_addr + (wg == 0 ? C_KA : C_VA), rowv);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(kv_tmem);
+    }
     const bool rec = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;
     for (int it = 0; it < nit; ++it) {
       if (rec) dbg[8 * it] = clock64();
@@ -770,7 +796,7 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
   const dim3 grid(B * H, (T + BKV - 1) / BKV);
   const float scale = 1.0f / sqrtf(static_cast<float>(HD));
   launch_pdl(attn_bwd_tc_kernel, dim3(grid), dim3(448), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
-                                                        scale, scale * 1.4426950408889634f, dq_acc, g_attn_dq_direct, g_attn_dbg);
+                                                        scale, scale * 1.4426950408889634f, dq_acc, g_attn_dq_direct, g_attn_kv_tmem, g_attn_dbg);
   const size_t n8 = rows * C / 8;
   launch_pdl(attn_dq_convert_kernel, dim3(static_cast<unsigned>((n8 + 255) / 256)), dim3(256), 0, stream, dq_acc, static_cast<__nv_bfloat16*>(dqkv), rows, C);
   count_launch(3);

@@ -16,3 +16,12 @@ def t(fn, n=20):
     return e0.elapsed_time(e1) / n * 1e3
 for _ in range(2):
     print(f"attention fwd {t(lambda: ops.attention_fwd(qkv, y, lse, B, T, H, D)):.1f} us   bwd (3 kernels) {t(lambda: ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc)):.1f} us")
+lib = _lib.load()
+ops.attention_fwd(qkv, y, lse, B, T, H, D)
+outs = {}
+for mode in (5, 6, 5, 6):
+    lib.nsb_attention_debug_config(mode)
+    us = t(lambda: ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc))
+    print("backward, K/V A operands from", "smem" if mode == 5 else "tmem", f"{us:.1f} us")
+    outs[mode] = dqkv.float().clone()
+print("max |diff| smem vs tmem variants:", (outs[5] - outs[6]).abs().max().item(), " ref max", outs[5].abs().max().item())
