@@ -33,6 +33,15 @@ FLOPS_PER_TOKEN = 854_770_176  # 6N + 12LHQT, SURVEY.md 8d
 NOMINAL_BF16 = 2.25e15
 
 
+def gemm_traffic_bytes():
+    """dram bytes per GEMM launch from the committed ncu capture of this workload (profiles/), or None."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01d_gemm_traffic.json")) as f:
+            return float(json.load(f)["dram_bytes_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -289,25 +298,36 @@ def main():
     ev = []
     orig_gemm = ops.gemm
 
+    ext_streams = {}
+
     def timed_gemm(M, N, K, *a, **k):
+        # events go on the stream the GEMM is launched on (the weight-gradient GEMMs run on a side stream)
+        h = k.get("stream")
+        if h is None or h == torch.cuda.current_stream().cuda_stream:
+            strm = torch.cuda.current_stream()
+        else:
+            strm = ext_streams.setdefault(h, torch.cuda.ExternalStream(h))
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
+        s.record(strm)
         orig_gemm(M, N, K, *a, **k)
-        e.record()
+        e.record(strm)
         ev.append((2.0 * M * N * K, s, e))
     import nanosandbox_b200.model as model_mod
     model_mod.ops.gemm = timed_gemm
+    keep_overlap = raw.overlap_wgrad
+    raw.overlap_wgrad = False   # one stream for this pass: each GEMM's events then bracket that GEMM alone
     try:
         train_step(resident, False)
         torch.cuda.synchronize()
     finally:
         model_mod.ops.gemm = orig_gemm
+        raw.overlap_wgrad = keep_overlap
     g_flops = sum(f for f, _, _ in ev)
     g_ms = sum(s.elapsed_time(e) for _, s, e in ev)
     achieved = g_flops / (g_ms / 1e3) / 1e12
     roofline = {"kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA bf16 GEMM, all layouts/epilogues)", "bound": "tensor",
                 "achieved": achieved, "peak": peaks["tf_sus"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sus"],
-                "traffic": None, "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json bf16_tflops_sustained: kernel timed inside a long step)",
+                "traffic": gemm_traffic_bytes(), "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json bf16_tflops_sustained: kernel timed inside a long step)",
                 "launches_timed": len(ev), "avg_launch_us": g_ms * 1e3 / max(1, len(ev)),
                 "algorithmic_flops_per_launch": g_flops / max(1, len(ev)),
                 "gemm_share_of_step": g_ms / (ms / args.steps)}
