@@ -176,12 +176,10 @@ __global__ void __launch_bounds__(192, 2)
   if (threadIdx.x == 0) {
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
     ptx::prefetch_tmap(&tmap_qkv);
-    ptx::mbar_init(q_full, 1);
-    for (int s = 0; s < KV_STAGES; ++s) { ptx::mbar_init(&kv_full[s], 1); ptx::mbar_init(&kv_empty[s], 1); }
-    ptx::mbar_init(s_full, 1);
-    ptx::mbar_init(p_full, 4);
-    ptx::mbar_init(o_full, 1);
-    ptx::mbar_init(pv_done, 1);
+  }
+  if (warp == 0 && lane < 9) {                       // one barrier per lane: q_full, kv_full[2], kv_empty[2], s_full, p_full, o_full, pv_done
+    static_assert(KV_STAGES == 2, "barrier layout");
+    ptx::mbar_init(&bars[lane], lane == 6 ? 4u : 1u);   // p_full collects the four softmax warps
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
@@ -451,7 +449,7 @@ __global__ void __launch_bounds__(448, 1)
   uint64_t* dkv_full = bars + 11;
   uint64_t* sdp_free = bars + 12;    // S^T / dP^T read into registers (TMEM columns reusable)  count 8
   uint64_t* kv_tmem = bars + 13;     // K / V rows copied into tensor memory             count 8
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
   float* stat = reinterpret_cast<float*>(smem + OFF_STAT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -467,15 +465,11 @@ __global__ void __launch_bounds__(448, 1)
     ptx::prefetch_tmap(&tmap_qkv);
     ptx::prefetch_tmap(&tmap_dy);
     ptx::prefetch_tmap(&tmap_dq);
-    ptx::mbar_init(kv_full, 1);
-    for (int s = 0; s < QS; ++s) { ptx::mbar_init(&qdo_full[s], 1); ptx::mbar_init(&qdo_empty[s], 1); }
-    ptx::mbar_init(sdp_full, 1);
-    ptx::mbar_init(pds_full, 8);
-    ptx::mbar_init(dq_full, 1);
-    ptx::mbar_init(dq_free, 4);
-    ptx::mbar_init(dkv_full, 1);
-    ptx::mbar_init(kv_tmem, 8);
-    ptx::mbar_init(sdp_free, 8);
+  }
+  if (warp == 0 && lane < 14) {                      // one barrier per lane (layout above)
+    static_assert(QS == 3, "barrier layout");
+    const uint32_t count = (lane == 8 || lane == 12 || lane == 13) ? 8u : (lane == 10 ? 4u : 1u);
+    ptx::mbar_init(&bars[lane], count);
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);

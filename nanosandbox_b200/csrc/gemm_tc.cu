@@ -257,18 +257,16 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       if (ep.kind == NSB_EPI_GELU) ptx::prefetch_tmap(&tma_c2);
       if (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU) ptx::prefetch_tmap(&tma_aux);
     }
-    for (int s = 0; s < stages; ++s) {
-      ptx::mbar_init(&full[s], 1);
-      ptx::mbar_init(&empty[s], 1);
-    }
-    for (int s = 0; s < 2; ++s) {
-      ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 4 * ngroups * CG);   // epilogue warps of both CTAs release the leader
-    }
-    for (int s = 0; s < kMaxBuf; ++s) {
-      ptx::mbar_init(&auxfull[s], 1);
-      ptx::mbar_init(&staged[s], 128);
-      ptx::mbar_init(&freeb[s], 1);
+  }
+  if (warp == 0) {
+    // the 44 barriers are initialised by the lanes of one warp side by side (a single thread doing it
+    // in turn was most of the CTA's set-up time)
+    constexpr int kBars = 2 * kMaxStages + 4 + 3 * kMaxBuf;
+    for (int i = lane; i < kBars; i += 32) {
+      uint32_t count = 1;                                                   // full, empty, tfull, auxfull, freeb
+      if (i >= 2 * kMaxStages + 2 && i < 2 * kMaxStages + 4) count = 4 * ngroups * CG;   // tempty: epilogue warps of both CTAs
+      else if (i >= 2 * kMaxStages + 4 + kMaxBuf && i < 2 * kMaxStages + 4 + 2 * kMaxBuf) count = 128;  // staged
+      ptx::mbar_init(&bars[i], count);
     }
     ptx::fence_mbar_init();
   }
