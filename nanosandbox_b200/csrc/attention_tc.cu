@@ -459,6 +459,14 @@ __global__ void __launch_bounds__(448, 1)
   const int nq = (Tn + BQ - 1) / BQ;
   const int nit = nq - jb;                         // query blocks jb .. nq-1
   const int row_base = b * Tn;
+  long long* rec3 = dbg != nullptr ? dbg + 1024 + 3 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
+  if (rec3 != nullptr && threadIdx.x == 0) {       // per-CTA trace: start ns, end ns, SM id
+    unsigned long long tns; unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tns));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    rec3[0] = static_cast<long long>(tns);
+    rec3[2] = smid;
+  }
 
   if (threadIdx.x == 0) {
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
@@ -717,6 +725,11 @@ __global__ void __launch_bounds__(448, 1)
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem, TMEM_COLS);
+  if (rec3 != nullptr && threadIdx.x == 0) {
+    unsigned long long tns;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tns));
+    rec3[1] = static_cast<long long>(tns);
+  }
 }
 
 // dq (bf16, inside dqkv) = dq_acc (fp32); dq_acc is zeroed again for the next call

@@ -30,7 +30,7 @@ def run(cmd, cwd, timeout=600):
 
 
 def prepare(tmp_path):
-    for f in ("train.py", "configurator.py", "model.py"):
+    for f in ("train.py", "configurator.py", "model.py", "sample.py"):
         os.symlink(os.path.join(ROOT, f), tmp_path / f)
     os.symlink(os.path.join(ROOT, "config"), tmp_path / "config")
 
@@ -54,6 +54,10 @@ def test_single_gpu_train_eval_checkpoint_resume(tmp_path):
     assert "Resuming training from out" in out2
     ls2 = losses(out2)
     assert ls2 and ls2[0] < ls[0] - 0.3        # picks up where it left off
+    # sample.py on that checkpoint (the synthetic stream's meta.pkl has no character table: prompt and samples are ids)
+    out_s = run([sys.executable, "sample.py", "--out_dir=out", "--num_samples=2", "--max_new_tokens=24", "--top_k=10",
+                 "--start=1 2 3"], tmp_path)
+    assert out_s.count("---------------") == 2
     # float32 (exact parity mode) runs through the same script
     out3 = run([sys.executable, "train.py", *COMMON, "--max_iters=10", "--out_dir=out32", "--dtype=float32"], tmp_path)
     assert losses(out3)

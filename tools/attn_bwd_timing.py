@@ -27,3 +27,17 @@ for it in range(8):
 print("mma warp per iteration: [top, pds_full seen, sdp_free seen (before S/dP of the next block is issued), dq_free seen]")
 for it in range(8):
     print(it, [x - t0 for x in d[512 + 4 * it:512 + 4 * it + 4]])
+
+import collections
+tr = dbg.cpu()[1024:1024 + 3 * 1152].view(1152, 3)
+t_min = int(tr[:, 0].min()); t_max = int(tr[:, 1].max())
+print("kernel span us", (t_max - t_min) / 1e3)
+dur = (tr[:, 1] - tr[:, 0]).float() / 1e3
+for jb in range(8):
+    sel = dur[jb * 144:(jb + 1) * 144]
+    st = (tr[jb * 144:(jb + 1) * 144, 0] - t_min).float() / 1e3
+    print(f"key block {jb}: {8 - jb} query blocks, CTA duration us mean {sel.mean():.2f} min {sel.min():.2f} max {sel.max():.2f} | start us min {st.min():.2f} max {st.max():.2f}")
+busy = collections.defaultdict(float)
+for i in range(1152):
+    busy[int(tr[i, 2])] += float(dur[i])
+print("per-SM sum of CTA durations us: min %.1f max %.1f mean %.1f" % (min(busy.values()), max(busy.values()), sum(busy.values()) / len(busy)))
