@@ -58,7 +58,13 @@ __device__ __forceinline__ float softmax_pass(uint32_t s_addr, uint8_t* sP, int 
     float* cur = (c & 1) ? vb : va;
     float* nxt = (c & 1) ? va : vb;
     if (c < 3) ptx::tmem_ld_32x32_async(s_addr + (c + 1) * 32, nxt);
-    if (DIAG) {
+    // diagonal block: the mask is decided per 32 x 32 sub-block (uniform over the warp's 32 query rows):
+    // key chunks left of the diagonal take the unmasked path below, the chunk the diagonal crosses masks
+    // per element, chunks right of it are zeros without any exp
+    if (DIAG && c > (row >> 5)) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) cur[i] = 0.f;
+    } else if (DIAG && c == (row >> 5)) {
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         if (c * 32 + i <= lim) mx = fmaxf(mx, cur[i]);
@@ -112,6 +118,7 @@ __device__ __forceinline__ float softmax_block(uint32_t s_addr, uint8_t* sP, int
     mx = -INFINITY;
 #pragma unroll 1
     for (int c = 0; c < 4; ++c) {
+      if (DIAG && c > (row >> 5)) break;             // key chunks right of the diagonal (warp-uniform)
       ptx::tmem_ld_32x32(s_addr + c * 32, va);
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
