@@ -169,7 +169,27 @@ def run_reference(args):
             "config": {"workload": WORKLOAD},
             "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": tok_s, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_RESULT_OUT = None
+
+
+def keep_stdout_clean():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL's version banner, warnings
+    from native code), so file descriptor 1 is pointed at stderr for the run and the result line goes to a
+    private duplicate of the original stdout."""
+    global _RESULT_OUT
+    if _RESULT_OUT is None:
+        sys.stdout.flush()
+        _RESULT_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _RESULT_OUT if _RESULT_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
@@ -182,6 +202,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-torch-baseline", action="store_true")
     args = ap.parse_args()
+    keep_stdout_clean()
     if args.impl == "reference":
         return run_reference(args)
     if not torch.cuda.is_available():
@@ -204,9 +225,6 @@ def main():
     torch.cuda.set_device(dev)
     ddp = world > 1
     if ddp:
-        # keep stdout to the one JSON line (NCCL prints its version banner there at VERSION level)
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group(backend="nccl", device_id=dev)
     assert ACCUM_TOTAL % world == 0
     accum = ACCUM_TOTAL // world
@@ -399,7 +417,7 @@ def main():
         }
         if comm is not None:
             line["allreduce"] = comm
-        print(json.dumps(line), flush=True)
+        emit(line)
     if ddp:
         dist.destroy_process_group()
 
