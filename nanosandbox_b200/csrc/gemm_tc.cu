@@ -690,14 +690,13 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
                 for (int j = 0; j < 4; ++j) {
                   const uint4 hr = hraw[half * 4 + j];
                   const float2 h0 = unpack_bf16x2(hr.x), h1 = unpack_bf16x2(hr.y), h2 = unpack_bf16x2(hr.z), h3 = unpack_bf16x2(hr.w);
-                  v[8 * j] = round_bf16(v[8 * j]) * gelu_fast_grad(h0.x);
-                  v[8 * j + 1] = round_bf16(v[8 * j + 1]) * gelu_fast_grad(h0.y);
-                  v[8 * j + 2] = round_bf16(v[8 * j + 2]) * gelu_fast_grad(h1.x);
-                  v[8 * j + 3] = round_bf16(v[8 * j + 3]) * gelu_fast_grad(h1.y);
-                  v[8 * j + 4] = round_bf16(v[8 * j + 4]) * gelu_fast_grad(h2.x);
-                  v[8 * j + 5] = round_bf16(v[8 * j + 5]) * gelu_fast_grad(h2.y);
-                  v[8 * j + 6] = round_bf16(v[8 * j + 6]) * gelu_fast_grad(h3.x);
-                  v[8 * j + 7] = round_bf16(v[8 * j + 7]) * gelu_fast_grad(h3.y);
+                  const float2 hh[4] = {h0, h1, h2, h3};
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const float2 g2 = gelu_fast_grad_mul2(hh[i].x, hh[i].y, round_bf16(v[8 * j + 2 * i]), round_bf16(v[8 * j + 2 * i + 1]));
+                    v[8 * j + 2 * i] = g2.x;
+                    v[8 * j + 2 * i + 1] = g2.y;
+                  }
                 }
               }
 #pragma unroll
@@ -718,7 +717,11 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
                 for (int j = 0; j < 4; ++j) {
                   float y[8];
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) y[i] = gelu_fast(round_bf16(v[8 * j + i]));
+                  for (int i = 0; i < 8; i += 2) {
+                    const float2 g2 = gelu_fast2(round_bf16(v[8 * j + i]), round_bf16(v[8 * j + i + 1]));
+                    y[i] = g2.x;
+                    y[i + 1] = g2.y;
+                  }
                   *reinterpret_cast<uint4*>(buf + stg_off(row, half * 4 + j)) =
                       make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
                 }

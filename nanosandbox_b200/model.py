@@ -184,7 +184,7 @@ class GPT(nn.Module):
         self._grad_sync = None          # set by nanosandbox_b200.ddp.DistributedDataParallel
         # bf16 path: GELU as its own memory-bound kernels (faster on B200 than the fused GEMM epilogues,
         # whose eight epilogue warps cannot hide the erf math behind a K = 768 mainloop)
-        self.split_gelu = True
+        self.split_gelu = os.environ.get("NSB_SPLIT_GELU", "1") != "0"
         # Training forward (bf16): the loss kernel also leaves softmax - onehot in the logits buffer (one
         # pass over the 1.2 GB of logits instead of two), so the `logits` returned next to the loss then
         # hold that gradient, not the logits.  Set to False if you read the logits of a training forward.
