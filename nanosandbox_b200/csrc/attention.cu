@@ -563,8 +563,9 @@ extern "C" {
 // memory + TMA reduce-add (the default) / reduced straight from registers
 void nsb_attention_debug_config(int force_simt) {
   if (force_simt == 3 || force_simt == 4) { attention_tc_set_dq_direct(force_simt == 4); g_attn_force_simt = 0; return; }
-  // 5 / 6: tensor-core backward with K, V read from shared memory (the default) / from tensor memory
+  // 5 / 6: tensor-core backward with every A operand from shared memory / K, V from tensor memory
   if (force_simt == 5 || force_simt == 6) { attention_tc_set_kv_tmem(force_simt == 6); g_attn_force_simt = 0; return; }
+  if (force_simt == 9) { attention_tc_set_kv_tmem(2); g_attn_force_simt = 0; return; }   // P^T in tensor memory for dV (the default)
   g_attn_force_simt = force_simt;
 }
 // device buffer (>= 1024 int64) receiving phase timestamps of one CTA of the tcgen05 kernels; NULL = off

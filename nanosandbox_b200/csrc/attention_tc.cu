@@ -333,7 +333,9 @@ static long long* g_attn_dbg = nullptr;
 void attention_tc_set_debug_buffer(long long* p) { g_attn_dbg = p; }
 static int g_attn_dq_direct = 0;   // 1: dQ leaves by vector reductions from registers (measured slower: 184 vs 156 us); 0: staged TMA reduce-add
 void attention_tc_set_dq_direct(int on) { g_attn_dq_direct = on; }
-static int g_attn_kv_tmem = 0;     // 1: K / V as tensor-memory A operands of the S^T / dP^T MMAs (bit-identical, measured no faster: the compute warps are the critical path)
+// 0: every A operand from shared memory; 1: K / V as tensor-memory A operands of the S^T / dP^T MMAs (bit-identical,
+// measured no faster); 2: P^T kept in tensor memory for the dV MMA (halves the probability warps' shared-memory stores)
+static int g_attn_kv_tmem = 2;
 void attention_tc_set_kv_tmem(int on) { g_attn_kv_tmem = on; }
 
 int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, int H, cudaStream_t stream) {
@@ -527,12 +529,12 @@ __global__ void __launch_bounds__(448, 1)
       if (ptx::elect_one()) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          if (kv_in_tmem) ptx::umma_bf16_ts(tmem + C_S, tmem + C_KA + 8 * k, q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+          if (kv_in_tmem == 1) ptx::umma_bf16_ts(tmem + C_S, tmem + C_KA + 8 * k, q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
           else ptx::umma_bf16(tmem + C_S, dK_ + static_cast<uint64_t>(2 * k), q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          if (kv_in_tmem) ptx::umma_bf16_ts(tmem + C_DP, tmem + C_VA + 8 * k, do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+          if (kv_in_tmem == 1) ptx::umma_bf16_ts(tmem + C_DP, tmem + C_VA + 8 * k, do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
           else ptx::umma_bf16(tmem + C_DP, dV_ + static_cast<uint64_t>(2 * k), do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
         }
         ptx::umma_commit(sdp_full);
@@ -540,7 +542,7 @@ __global__ void __launch_bounds__(448, 1)
       __syncwarp();
     };
     ptx::mbar_wait(kv_full, 0);
-    if (kv_in_tmem) ptx::mbar_wait(kv_tmem, 0);
+    if (kv_in_tmem == 1) ptx::mbar_wait(kv_tmem, 0);
     ptx::mbar_wait(&qdo_full[0], 0);
     ptx::tc_fence_after();
     issue_sdp(0);
@@ -566,7 +568,8 @@ __global__ void __launch_bounds__(448, 1)
 #pragma unroll
         for (int k = 0; k < 8; ++k) {  // K = 128 queries: A atom k/4, 32 B per step inside; B 16 q rows = 2048 B per step
           const uint64_t a_off = static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4);
-          ptx::umma_bf16(tmem + C_DV, dPT + a_off, do_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+          if (kv_in_tmem == 2) ptx::umma_bf16_ts(tmem + C_DV, tmem + C_KA + 8 * k, do_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+          else ptx::umma_bf16(tmem + C_DV, dPT + a_off, do_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
         }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -653,7 +656,7 @@ __global__ void __launch_bounds__(448, 1)
       return ct < 128 ? -lse_g[qg] * 1.4426950408889634f : -del_g[qg];   // negated: see bwd_probs
     };
     float st_next = load_stat(0);
-    if (kv_in_tmem) {
+    if (kv_in_tmem == 1) {
       // this thread's key row of K (group 0) or V (group 1): swizzled smem -> registers -> tensor memory,
       // where the S^T / dP^T MMAs read it as their A operand for the whole loop
       ptx::mbar_wait(kv_full, 0);
@@ -697,10 +700,20 @@ __global__ void __launch_bounds__(448, 1)
       if (rec) dbg[8 * it + 3] = clock64();
       uint8_t* pt = smem + OFF_PT + wg * TILE;
       uint8_t* dst = smem + OFF_DS + wg * TILE;
+      if (kv_in_tmem == 2) {
+        // P^T stays in tensor memory (this thread's key row, 32 packed columns of its 64 queries) and is the
+        // A operand of the dV MMA from there; only dS^T (read twice, once transposed) goes to shared memory
+        ptx::tmem_st_32x32_u32(tmem + lane_addr + C_KA + wg * 32, pk);
+        ptx::tc_fence_before();
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        *reinterpret_cast<uint4*>(pt + sw128(row, i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
-        *reinterpret_cast<uint4*>(dst + sw128(row, i)) = make_uint4(dk[4 * i], dk[4 * i + 1], dk[4 * i + 2], dk[4 * i + 3]);
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<uint4*>(dst + sw128(row, i)) = make_uint4(dk[4 * i], dk[4 * i + 1], dk[4 * i + 2], dk[4 * i + 3]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          *reinterpret_cast<uint4*>(pt + sw128(row, i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          *reinterpret_cast<uint4*>(dst + sw128(row, i)) = make_uint4(dk[4 * i], dk[4 * i + 1], dk[4 * i + 2], dk[4 * i + 3]);
+        }
       }
       ptx::fence_proxy_async();
       __syncwarp();
