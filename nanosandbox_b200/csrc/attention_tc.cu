@@ -29,6 +29,7 @@ constexpr int KV_STAGES = 2;
 constexpr int SMEM_BYTES = TILE + KV_STAGES * 2 * TILE + P_BYTES + 256;
 constexpr uint32_t TMEM_COLS = 256;        // S: 128 columns, O block: 64 columns
 constexpr uint32_t S_COL = 0, O_COL = 128;
+constexpr uint32_t P_COL = 192;            // P as bf16 pairs (64 columns) when it is kept in tensor memory for P V
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -46,7 +47,7 @@ __device__ __forceinline__ uint32_t sw128(int row, int q16) {
 // 32-column chunk is in flight while the current one is processed.
 template <bool DIAG>
 __device__ __forceinline__ float softmax_pass(uint32_t s_addr, uint8_t* sP, int row, int lim, float scale_log2,
-                                              float m, float& mx, uint64_t* pv_bar, uint32_t pv_parity) {
+                                              float m, float& mx, uint64_t* pv_bar, uint32_t pv_parity, uint32_t p_tmem) {
   using namespace fatc;
   float va[32], vb[32];
   float s0 = 0.f, s1 = 0.f;
@@ -92,13 +93,22 @@ __device__ __forceinline__ float softmax_pass(uint32_t s_addr, uint8_t* sP, int 
     uint8_t* atom = sP + (c >> 1) * TILE;
     // the previous block's P V may still be reading this tile: wait right before the first store
     if (c == 0 && pv_bar != nullptr) ptx::mbar_wait(pv_bar, pv_parity);
+    if (p_tmem != 0) {
+      // P stays in tensor memory (this query row, 16 packed columns per 32 keys): A operand of P V from there
+      uint32_t pw[16];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-      *reinterpret_cast<uint4*>(atom + sw128(row, (c & 1) * 4 + i)) =
-          make_uint4(pack_bf16x2(cur[8 * i], cur[8 * i + 1]), pack_bf16x2(cur[8 * i + 2], cur[8 * i + 3]),
-                     pack_bf16x2(cur[8 * i + 4], cur[8 * i + 5]), pack_bf16x2(cur[8 * i + 6], cur[8 * i + 7]));
+      for (int i = 0; i < 16; ++i) pw[i] = pack_bf16x2(cur[2 * i], cur[2 * i + 1]);
+      ptx::tmem_st_32x16_u32_nowait(p_tmem + c * 16, pw);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(atom + sw128(row, (c & 1) * 4 + i)) =
+            make_uint4(pack_bf16x2(cur[8 * i], cur[8 * i + 1]), pack_bf16x2(cur[8 * i + 2], cur[8 * i + 3]),
+                       pack_bf16x2(cur[8 * i + 4], cur[8 * i + 5]), pack_bf16x2(cur[8 * i + 6], cur[8 * i + 7]));
+    }
     if (c < 3) ptx::tmem_wait_ld32(nxt);
   }
+  if (p_tmem != 0) ptx::tmem_wait_st();
   return s0 + s1;
 }
 
@@ -108,10 +118,11 @@ __device__ __forceinline__ float softmax_pass(uint32_t s_addr, uint8_t* sP, int 
 // softmax is shift invariant; P stays below 2^8.  Returns the O rescale factor (1 = none).
 template <bool DIAG>
 __device__ __forceinline__ float softmax_block(uint32_t s_addr, uint8_t* sP, int row, int lim, float scale_log2,
-                                               float& m, float& l, bool first, uint64_t* pv_bar, uint32_t pv_parity) {
+                                               float& m, float& l, bool first, uint64_t* pv_bar, uint32_t pv_parity,
+                                               uint32_t p_tmem) {
   float mx;
   float sum = 0.f;
-  if (!first) sum = softmax_pass<DIAG>(s_addr, sP, row, lim, scale_log2, m, mx, pv_bar, pv_parity);
+  if (!first) sum = softmax_pass<DIAG>(s_addr, sP, row, lim, scale_log2, m, mx, pv_bar, pv_parity, p_tmem);
   else {
     // first block: only the maximum is needed (m = -inf would make every P infinite)
     float va[32];
@@ -138,7 +149,7 @@ __device__ __forceinline__ float softmax_block(uint32_t s_addr, uint8_t* sP, int
     }
     float dummy;
     // (a repeated pass finds the previous P V retired already: the first pass waited for it)
-    sum = softmax_pass<DIAG>(s_addr, sP, row, lim, scale_log2, m, dummy, nullptr, 0);
+    sum = softmax_pass<DIAG>(s_addr, sP, row, lim, scale_log2, m, dummy, nullptr, 0, p_tmem);
   }
   l += sum;
   return corr;
@@ -148,7 +159,7 @@ __device__ __forceinline__ float softmax_block(uint32_t s_addr, uint8_t* sP, int
 // block at dbg[0..], the MMA thread 4 stamps per block at dbg[512..].  NULL in production.
 __global__ void __launch_bounds__(192, 2)
     attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ y,
-                       float* __restrict__ lse, int Tn, int H, float scale_log2, long long* dbg) {
+                       float* __restrict__ lse, int Tn, int H, float scale_log2, int p_in_tmem, long long* dbg) {
   using namespace fatc;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sQ = smem;
@@ -253,8 +264,10 @@ __global__ void __launch_bounds__(192, 2)
         if (ptx::elect_one()) {
 #pragma unroll
           for (int k = 0; k < BKV / 16; ++k)
-            ptx::umma_bf16(tmem + O_COL, p_desc0 + static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4),
-                           v_desc + static_cast<uint64_t>(128 * k), IDESC_O, (j > 0 || k > 0) ? 1u : 0u);
+            if (p_in_tmem) ptx::umma_bf16_ts(tmem + O_COL, tmem + P_COL + 8 * k, v_desc + static_cast<uint64_t>(128 * k), IDESC_O,
+                                             (j > 0 || k > 0) ? 1u : 0u);
+            else ptx::umma_bf16(tmem + O_COL, p_desc0 + static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4),
+                                v_desc + static_cast<uint64_t>(128 * k), IDESC_O, (j > 0 || k > 0) ? 1u : 0u);
           ptx::umma_commit(pv_done);                // P smem may be overwritten
           ptx::umma_commit(&kv_empty[s]);           // K/V stage may be refilled
           if (j == nblk - 1) ptx::umma_commit(o_full);
@@ -270,6 +283,7 @@ __global__ void __launch_bounds__(192, 2)
     const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
     float m = -INFINITY, l = 0.f;
     const uint32_t s_addr = tmem + lane_addr + S_COL, o_addr = tmem + lane_addr + O_COL;
+    const uint32_t p_addr = p_in_tmem ? tmem + lane_addr + P_COL : 0u;
     const bool rec = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;
     for (int j = 0; j < nblk; ++j) {
       // S_j is ready; P V of block j-1 may still be running (pv_done is awaited before P is overwritten)
@@ -279,8 +293,8 @@ __global__ void __launch_bounds__(192, 2)
       if (rec) dbg[4 * j + 1] = clock64();
       uint64_t* pvb = j > 0 ? pv_done : nullptr;
       const uint32_t pvp = static_cast<uint32_t>((j - 1) & 1);
-      const float corr = (j == qb) ? softmax_block<true>(s_addr, sP, row, qi - j * BKV, scale_log2, m, l, j == 0, pvb, pvp)
-                                   : softmax_block<false>(s_addr, sP, row, 0, scale_log2, m, l, j == 0, pvb, pvp);
+      const float corr = (j == qb) ? softmax_block<true>(s_addr, sP, row, qi - j * BKV, scale_log2, m, l, j == 0, pvb, pvp, p_addr)
+                                   : softmax_block<false>(s_addr, sP, row, 0, scale_log2, m, l, j == 0, pvb, pvp, p_addr);
       if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
         // rare: this warp's rows rescale their O accumulator in TMEM (warp-uniform branch)
         float v[32];
@@ -330,6 +344,8 @@ __global__ void __launch_bounds__(192, 2)
 }
 
 static long long* g_attn_dbg = nullptr;
+static int g_attn_fwd_p_tmem = 1;  // forward: P kept in tensor memory for the P V MMA (0: through shared memory)
+void attention_tc_set_fwd_p_tmem(int on) { g_attn_fwd_p_tmem = on; }
 void attention_tc_set_debug_buffer(long long* p) { g_attn_dbg = p; }
 static int g_attn_dq_direct = 0;   // 1: dQ leaves by vector reductions from registers (measured slower: 184 vs 156 us); 0: staged TMA reduce-add
 void attention_tc_set_dq_direct(int on) { g_attn_dq_direct = on; }
@@ -353,7 +369,7 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
   }
   const dim3 grid(B * H, (T + BQ - 1) / BQ);
   launch_pdl(attn_fwd_tc_kernel, dim3(grid), dim3(192), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
-                                                        1.4426950408889634f / sqrtf(static_cast<float>(HD)), g_attn_dbg);
+                                                        1.4426950408889634f / sqrtf(static_cast<float>(HD)), g_attn_fwd_p_tmem, g_attn_dbg);
   count_launch();
   return check_launch("attention_fwd_tc");
 }

@@ -291,6 +291,17 @@ __device__ __forceinline__ void tmem_st_32x32_u32(uint32_t taddr, const uint32_t
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
+// 16 packed words per thread, no wait: follow a batch of these with tmem_wait_st()
+__device__ __forceinline__ void tmem_st_32x16_u32_nowait(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+      "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 // ---- UMMA descriptors -----------------------------------------------------------------------
 // shared-memory matrix descriptor, 128-byte swizzle.  Units of 16 bytes for addr/LBO/SBO.
 __device__ __forceinline__ uint64_t umma_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes,
