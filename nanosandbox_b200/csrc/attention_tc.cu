@@ -16,6 +16,10 @@
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
+#ifndef NSB_ATTN_POLY_OF8
+#define NSB_ATTN_POLY_OF8 0   // measured: every share above 0 is slower (54.0 us at 0, 56.7 at 3, 59.8 at 5): the loop is issue-bound, not MUFU-bound
+#endif
+
 namespace nsb {
 
 int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint64_t d1, uint64_t row_stride,
@@ -29,6 +33,7 @@ constexpr int KV_STAGES = 2;
 constexpr int SMEM_BYTES = TILE + KV_STAGES * 2 * TILE + P_BYTES + 256;
 constexpr uint32_t TMEM_COLS = 256;        // S: 128 columns, O block: 64 columns
 constexpr uint32_t S_COL = 0, O_COL = 128;
+constexpr int kPolyOf8 = NSB_ATTN_POLY_OF8;   // share of the forward softmax's exp2 done by polynomial (0..8 of 8)
 constexpr uint32_t P_COL = 192;            // P as bf16 pairs (64 columns) when it is kept in tensor memory for P V
 
 __device__ __forceinline__ float ex2(float x) {
@@ -84,8 +89,10 @@ __device__ __forceinline__ float softmax_pass(uint32_t s_addr, uint8_t* sP, int 
         mx = max3(mx, cur[i], cur[i + 1]);
         float a0, a1;
         unpack2(fma2(pack2(cur[i], cur[i + 1]), sc2, nm2), a0, a1);
-        cur[i] = ex2(a0);
-        cur[i + 1] = ex2(a1);
+        // kPolyOf8 of every 8 column pairs take their exp2 on the FMA pipe (ex2_poly2), the rest on the
+        // special-function unit, which one exp per score would otherwise saturate
+        if (((i >> 1) & 7) < kPolyOf8) ex2_poly2(a0, a1, cur[i], cur[i + 1]);
+        else { cur[i] = ex2(a0); cur[i + 1] = ex2(a1); }
         acc = add2(acc, pack2(cur[i], cur[i + 1]));
       }
       unpack2(acc, s0, s1);

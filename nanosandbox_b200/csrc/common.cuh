@@ -117,6 +117,25 @@ __device__ __forceinline__ void unpack2(f32x2 x, float& a, float& b) { asm("mov.
 __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
 __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
 __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+// 2^x for two values on the fp32 FMA pipe instead of the special-function unit (which a softmax loop
+// saturates at one exp per score): round-to-nearest split x = n + f, |f| <= 0.5, 2^f by a degree-4 minimax
+// polynomial (max relative error 2.7e-6), n added into the exponent field.  x is clamped at -126 (result
+// ~1e-38 instead of 0); x must stay below 127.
+__device__ __forceinline__ void ex2_poly2(float x0, float x1, float& y0, float& y1) {
+  const f32x2 magic = pack2(12582912.f, 12582912.f), nmagic = pack2(-12582912.f, -12582912.f);
+  const f32x2 x = pack2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
+  const f32x2 t = add2(x, magic);                       // low mantissa bits of t = round(x) (two's complement)
+  const f32x2 f = fma2(add2(t, nmagic), pack2(-1.f, -1.f), x);
+  f32x2 p = fma2(pack2(0.009570102207362652f, 0.009570102207362652f), f, pack2(0.05591785907745361f, 0.05591785907745361f));
+  p = fma2(p, f, pack2(0.240247443318367f, 0.240247443318367f));
+  p = fma2(p, f, pack2(0.6931217908859253f, 0.6931217908859253f));
+  p = fma2(p, f, pack2(0.9999992847442627f, 0.9999992847442627f));
+  float p0, p1, t0, t1;
+  unpack2(p, p0, p1);
+  unpack2(t, t0, t1);
+  y0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+  y1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
 __device__ __forceinline__ float max3(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
 // Phi(x0), Phi(x1) and the two unscaled densities exp(-x^2/2)
 __device__ __forceinline__ void gelu_fast_parts2(float x0, float x1, float& cdf0, float& cdf1, f32x2& pdf_unscaled) {
