@@ -1,4 +1,5 @@
-cp nanosandbox_b200/lib/libnanosandbox_b200.so /tmp/keep.so
-for v in 0 2 3 4 5 0 3; do cp nanosandbox_b200/lib/ab_$v.so nanosandbox_b200/lib/libnanosandbox_b200.so; echo "poly $v of 8: $(PYTHONPATH=. python tools/attn_ab.py 2>&1 | head -2 | tail -1)"; done
-cp /tmp/keep.so nanosandbox_b200/lib/libnanosandbox_b200.so
-timeout 300 python -m pytest tests/test_kernels_gpu.py -m gpu -x -q -k attention 2>&1 | tail -2
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+timeout 600 python bench.py --steps 4 --warmup 3 > gpurun_out/bench_r1_v8.json 2> gpurun_out/bench_v8.err
+wc -l gpurun_out/bench_r1_v8.json
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 37000 -c 700 --csv --log-file gpurun_out/launches_r01f.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-torch-baseline > gpurun_out/ncu8.log 2>&1
