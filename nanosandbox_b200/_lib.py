@@ -88,6 +88,8 @@ def load() -> C.CDLL:
             fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
             fn.restype = res
             fn.argtypes = args
+    if os.environ.get("NSB_ATTN_MODE"):                # A/B switch: see nsb_attention_debug_config in attention.cu
+        lib.nsb_attention_debug_config(int(os.environ["NSB_ATTN_MODE"]))
     if os.environ.get("NSB_GEMM_PDL", "1") == "0":  # A/B switch for the dependent-launch overlap
         lib.nsb_gemm_debug_pdl(0)
     _lib = lib

@@ -354,6 +354,8 @@ static long long* g_attn_dbg = nullptr;
 static int g_attn_fwd_p_tmem = 1;  // forward: P kept in tensor memory for the P V MMA (0: through shared memory)
 void attention_tc_set_fwd_p_tmem(int on) { g_attn_fwd_p_tmem = on; }
 void attention_tc_set_debug_buffer(long long* p) { g_attn_dbg = p; }
+static int g_attn_bwd_warps16 = 1;  // backward with 16 probability warps (attn_bwd_tc16_kernel); 0: the 8-warp kernel
+void attention_tc_set_bwd_warps16(int on) { g_attn_bwd_warps16 = on; }
 static int g_attn_dq_direct = 0;   // 1: dQ leaves by vector reductions from registers (measured slower: 184 vs 156 us); 0: staged TMA reduce-add
 void attention_tc_set_dq_direct(int on) { g_attn_dq_direct = on; }
 // 0: every A operand from shared memory; 1: K / V as tensor-memory A operands of the S^T / dP^T MMAs (bit-identical,
@@ -775,6 +777,282 @@ __global__ void __launch_bounds__(448, 1)
   }
 }
 
+// ---- backward with sixteen probability warps -------------------------------------------------------
+// Same algorithm and barrier protocol as attn_bwd_tc_kernel; the 128 x 128 block of probabilities is
+// spread over 16 warps (four groups of 32 query columns) instead of 8, so that every SM sub-partition has
+// four of them to overlap exp2, packed math, tensor-memory traffic and the dS^T stores, and each thread
+// works on 16 columns at a time (80 registers per thread at 704 threads).  P^T always lives in tensor memory.
+// Warps: 0 TMA, 1 MMA issue, 2..17 probabilities, 18..21 dQ write-back.
+template <bool MASK>
+__device__ __forceinline__ void bwd_probs16(uint32_t taddr, const float* nlse2, const float* ndlt, float scale_log2,
+                                            int col0, int row, int qlim, bool diag, uint32_t* pk, uint32_t* dk) {
+  using fatc::ex2;
+  float sv[16], dv[16];
+  ptx::tmem_ld_32x16_async(taddr + fabw::C_S, sv);
+  ptx::tmem_ld_32x16_async(taddr + fabw::C_DP, dv);
+  ptx::tmem_wait_ld16(sv);
+  ptx::tmem_wait_ld16(dv);
+  const f32x2 sc2 = pack2(scale_log2, scale_log2);
+#pragma unroll
+  for (int i = 0; i < 16; i += 4) {
+    const float4 l4 = *reinterpret_cast<const float4*>(nlse2 + i);
+    const float4 d4 = *reinterpret_cast<const float4*>(ndlt + i);
+    const float nl[4] = {l4.x, l4.y, l4.z, l4.w}, nd[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+    for (int e = 0; e < 4; e += 2) {
+      float a0, a1;
+      unpack2(fma2(pack2(sv[i + e], sv[i + e + 1]), sc2, pack2(nl[e], nl[e + 1])), a0, a1);
+      float p0 = ex2(a0), p1 = ex2(a1);
+      if (MASK) {
+        const int col = col0 + i + e;                          // query column within the block
+        p0 = ((col < qlim) && (!diag || col >= row)) ? p0 : 0.f;
+        p1 = ((col + 1 < qlim) && (!diag || col + 1 >= row)) ? p1 : 0.f;
+      }
+      float d0, d1;
+      unpack2(mul2(pack2(p0, p1), add2(pack2(dv[i + e], dv[i + e + 1]), pack2(nd[e], nd[e + 1]))), d0, d1);
+      pk[(i + e) >> 1] = pack_bf16x2(p0, p1);
+      dk[(i + e) >> 1] = pack_bf16x2(d0, d1);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(704, 1)
+    attn_bwd_tc16_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_dy,
+                         const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse,
+                         const float* __restrict__ delta, __nv_bfloat16* __restrict__ dqkv, int Tn, int H,
+                         float scale, float scale_log2) {
+  using namespace fabw;
+  using fatc::sw128;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* kv_full = bars;          // K, V landed
+  uint64_t* qdo_full = bars + 1;     // [QS] Q_i, dO_i landed
+  uint64_t* qdo_empty = bars + 4;    // [QS]
+  uint64_t* sdp_full = bars + 7;     // S^T, dP^T in TMEM
+  uint64_t* pds_full = bars + 8;     // P^T in TMEM, dS^T in smem                       count 16
+  uint64_t* dq_full = bars + 9;      // dV/dK/dQ MMAs of the block retired
+  uint64_t* dq_free = bars + 10;     // dQ columns read back                           count 4
+  uint64_t* dkv_full = bars + 11;
+  uint64_t* sdp_free = bars + 12;    // S^T / dP^T read into registers                  count 16
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  float* stat = reinterpret_cast<float*>(smem + OFF_STAT);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int C = H * HD;
+  const int jb = blockIdx.y;                       // key block; block 0 has the longest loop and starts first
+  const int bh = blockIdx.x, b = bh / H, h = bh % H;
+  const int nq = (Tn + BQ - 1) / BQ;
+  const int nit = nq - jb;                         // query blocks jb .. nq-1
+  const int row_base = b * Tn;
+
+  if (threadIdx.x == 0) {
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+    ptx::prefetch_tmap(&tmap_qkv);
+    ptx::prefetch_tmap(&tmap_dy);
+    ptx::prefetch_tmap(&tmap_dq);
+  }
+  if (warp == 0 && lane < 13) {
+    static_assert(QS == 3, "barrier layout");
+    const uint32_t count = (lane == 8 || lane == 12) ? 16u : (lane == 10 ? 4u : 1u);
+    ptx::mbar_init(&bars[lane], count);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  pdl_wait();
+  pdl_trigger();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(kv_full, 2 * TILE);
+      ptx::tma_load_2d(smem + OFF_K, &tmap_qkv, kv_full, C + h * HD, row_base + jb * BKV);
+      ptx::tma_load_2d(smem + OFF_V, &tmap_qkv, kv_full, 2 * C + h * HD, row_base + jb * BKV);
+      for (int it = 0; it < nit; ++it) {
+        const int s = it % QS;
+        ptx::mbar_wait(&qdo_empty[s], ((it / QS) & 1) ^ 1);
+        ptx::mbar_expect_tx(&qdo_full[s], 2 * TILE);
+        ptx::tma_load_2d(smem + OFF_Q + s * TILE, &tmap_qkv, &qdo_full[s], h * HD, row_base + (jb + it) * BQ);
+        ptx::tma_load_2d(smem + OFF_DO + s * TILE, &tmap_dy, &qdo_full[s], h * HD, row_base + (jb + it) * BQ);
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t ID_SDP = ptx::umma_idesc_bf16(128, 128, false, false);  // S^T, dP^T
+    constexpr uint32_t ID_DKV = ptx::umma_idesc_bf16(128, 64, false, true);    // dV, dK: B MN-major
+    constexpr uint32_t ID_DQ = ptx::umma_idesc_bf16(128, 64, true, true);      // dQ: A and B MN-major
+    const uint32_t sb = ptx::smem_u32(smem);
+    const uint64_t dK_ = ptx::umma_smem_desc_sw128(sb + OFF_K, 16, 1024);
+    const uint64_t dV_ = ptx::umma_smem_desc_sw128(sb + OFF_V, 16, 1024);
+    const uint64_t dKmn = ptx::umma_smem_desc_sw128(sb + OFF_K, TILE, 1024);
+    const uint64_t dDS = ptx::umma_smem_desc_sw128(sb + OFF_DS, 16, 1024);
+    const uint64_t dDSmn = ptx::umma_smem_desc_sw128(sb + OFF_DS, TILE, 1024);
+    auto issue_sdp = [&](int it) {
+      const int s = it % QS;
+      const uint64_t q_k = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, 16, 1024);
+      const uint64_t do_k = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, 16, 1024);
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tmem + C_S, dK_ + static_cast<uint64_t>(2 * k), q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tmem + C_DP, dV_ + static_cast<uint64_t>(2 * k), do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+        ptx::umma_commit(sdp_full);
+      }
+      __syncwarp();
+    };
+    ptx::mbar_wait(kv_full, 0);
+    ptx::mbar_wait(&qdo_full[0], 0);
+    ptx::tc_fence_after();
+    issue_sdp(0);
+    for (int it = 0; it < nit; ++it) {
+      const int s = it % QS;
+      if (it + 1 < nit) {
+        ptx::mbar_wait(sdp_free, it & 1);
+        ptx::mbar_wait(&qdo_full[(it + 1) % QS], ((it + 1) / QS) & 1);
+        ptx::tc_fence_after();
+        issue_sdp(it + 1);
+      }
+      ptx::mbar_wait(pds_full, it & 1);
+      ptx::tc_fence_after();
+      const uint64_t q_mn = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, TILE, 1024);
+      const uint64_t do_mn = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, TILE, 1024);
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)      // dV += P^T dO, A = P^T from tensor memory (8 packed columns per 16 queries)
+          ptx::umma_bf16_ts(tmem + C_DV, tmem + C_KA + 8 * k, do_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint64_t a_off = static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4);
+          ptx::umma_bf16(tmem + C_DK, dDS + a_off, q_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+        }
+      }
+      __syncwarp();
+      if (it > 0) { ptx::mbar_wait(dq_free, (it - 1) & 1); ptx::tc_fence_after(); }
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          ptx::umma_bf16(tmem + C_DQ, dDSmn + static_cast<uint64_t>(128 * k), dKmn + static_cast<uint64_t>(128 * k), ID_DQ, k > 0);
+        ptx::umma_commit(dq_full);
+        ptx::umma_commit(&qdo_empty[s]);
+        if (it == nit - 1) ptx::umma_commit(dkv_full);
+      }
+      __syncwarp();
+    }
+  } else if (warp >= 18) {
+    // ---- dQ write-back warps: TMEM (lane = query row) -> x scale -> swizzled smem -> TMA reduce-add ----
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;
+    const int et = threadIdx.x - 576;               // 0..127
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    for (int it = 0; it < nit; ++it) {
+      ptx::mbar_wait(dq_full, it & 1);
+      ptx::tc_fence_after();
+      float v[32];
+      ptx::tmem_ld_32x32(tmem + lane_addr + C_DQ, v);
+      if (et == 0) ptx::bulk_wait_read<0>();        // both staging atoms drained
+      ptx::named_bar_sync(1, 128);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<float4*>(smem + OFF_DQ + sw128(row, i)) =
+            make_float4(v[4 * i] * scale, v[4 * i + 1] * scale, v[4 * i + 2] * scale, v[4 * i + 3] * scale);
+      ptx::tmem_ld_32x32(tmem + lane_addr + C_DQ + 32, v);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(dq_free);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<float4*>(smem + OFF_DQ + TILE + sw128(row, i)) =
+            make_float4(v[4 * i] * scale, v[4 * i + 1] * scale, v[4 * i + 2] * scale, v[4 * i + 3] * scale);
+      ptx::fence_proxy_async();
+      ptx::named_bar_sync(1, 128);
+      if (et == 0) {
+        ptx::tma_reduce_add_2d(&tmap_dq, smem + OFF_DQ, h * HD, row_base + (jb + it) * BQ);
+        ptx::tma_reduce_add_2d(&tmap_dq, smem + OFF_DQ + TILE, h * HD + 32, row_base + (jb + it) * BQ);
+        ptx::bulk_commit();
+      }
+    }
+    if (et == 0) ptx::bulk_wait_all();
+  } else {
+    // ================================ probability warps (16) ================================
+    const int wg = (warp - 2) >> 2;                 // 0..3: query columns 32 wg .. 32 wg + 31 of a block
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;                 // TMEM lane: key row
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    const int key = jb * BKV + row;
+    const float* lse_g = lse + (static_cast<size_t>(b) * H + h) * Tn;
+    const float* del_g = delta + (static_cast<size_t>(b) * H + h) * Tn;
+    const int ct = threadIdx.x - 64;                // 0..511; the first 256 load the per-query statistics
+    auto load_stat = [&](int it) -> float {
+      const int qg = (jb + it) * BQ + (ct & 127);
+      if (ct >= 256 || qg >= Tn) return 0.f;
+      return ct < 128 ? -lse_g[qg] * 1.4426950408889634f : -del_g[qg];   // negated: see bwd_probs
+    };
+    float st_next = load_stat(0);
+    for (int it = 0; it < nit; ++it) {
+      if (ct < 256) stat[(it & 1) * 256 + ct] = st_next;
+      if (it + 1 < nit) st_next = load_stat(it + 1);
+      ptx::named_bar_sync(3, 512);
+      const float* nlse2 = stat + (it & 1) * 256 + wg * 32;
+      const float* ndlt = nlse2 + 128;
+      const bool diag = (it == 0);
+      const int qlim = Tn - (jb + it) * BQ;         // query columns >= qlim are padding
+      ptx::mbar_wait(sdp_full, it & 1);
+      ptx::tc_fence_after();
+      uint32_t pk[16], dk[16];                      // packed bf16 pairs of P^T and dS^T (32 columns)
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        const uint32_t ta = tmem + lane_addr + wg * 32 + hf * 16;
+        if (diag || qlim < BQ)
+          bwd_probs16<true>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8);
+        else
+          bwd_probs16<false>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(sdp_free);
+      // the P^T columns and the dS^T tile are free once the previous block's dV/dK/dQ MMAs have retired
+      if (it > 0) { ptx::mbar_wait(dq_full, (it - 1) & 1); ptx::tc_fence_after(); }
+      ptx::tmem_st_32x8_u32_nowait(tmem + lane_addr + C_KA + wg * 16, pk);
+      ptx::tmem_st_32x8_u32_nowait(tmem + lane_addr + C_KA + wg * 16 + 8, pk + 8);
+      uint8_t* dst = smem + OFF_DS + (wg >> 1) * TILE;
+      const int q0 = (wg & 1) * 4;                  // first 16-byte chunk of this group's 32 columns in the 128-byte row
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(dst + sw128(row, q0 + i)) = make_uint4(dk[4 * i], dk[4 * i + 1], dk[4 * i + 2], dk[4 * i + 3]);
+      ptx::tmem_wait_st();
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(pds_full);
+    }
+    // dK (groups 0, 1) / dV (groups 2, 3) of this key block, 32 of the 64 columns each
+    ptx::mbar_wait(dkv_full, 0);
+    ptx::tc_fence_after();
+    {
+      const bool live = key < Tn;
+      const bool is_dk = wg < 2;
+      const int c0 = (wg & 1) * 32;
+      const float f = is_dk ? scale : 1.f;
+      __nv_bfloat16* out = dqkv + (static_cast<size_t>(row_base) + (live ? key : 0)) * (3 * C) + (is_dk ? C : 2 * C) + h * HD + c0;
+      float v[32];
+      ptx::tmem_ld_32x32(tmem + lane_addr + (is_dk ? C_DK : C_DV) + c0, v);
+      if (live) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          reinterpret_cast<uint4*>(out)[i] =
+              make_uint4(pack_bf16x2(v[8 * i] * f, v[8 * i + 1] * f), pack_bf16x2(v[8 * i + 2] * f, v[8 * i + 3] * f),
+                         pack_bf16x2(v[8 * i + 4] * f, v[8 * i + 5] * f), pack_bf16x2(v[8 * i + 6] * f, v[8 * i + 7] * f));
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem, TMEM_COLS);
+}
+
 // dq (bf16, inside dqkv) = dq_acc (fp32); dq_acc is zeroed again for the next call
 __global__ void __launch_bounds__(256)
     attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, size_t M, int C) {
@@ -845,8 +1123,19 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
       static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H);
   const dim3 grid(B * H, (T + BKV - 1) / BKV);
   const float scale = 1.0f / sqrtf(static_cast<float>(HD));
-  launch_pdl(attn_bwd_tc_kernel, dim3(grid), dim3(448), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
-                                                        scale, scale * 1.4426950408889634f, dq_acc, g_attn_dq_direct, g_attn_kv_tmem, g_attn_dbg);
+  if (g_attn_bwd_warps16 && g_attn_dbg == nullptr) {
+    static bool attr16 = false;
+    if (!attr16) {
+      cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+      NSB_REQUIRE(e == cudaSuccess, "attention_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      attr16 = true;
+    }
+    launch_pdl(attn_bwd_tc16_kernel, dim3(grid), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta,
+               static_cast<__nv_bfloat16*>(dqkv), T, H, scale, scale * 1.4426950408889634f);
+  } else {
+    launch_pdl(attn_bwd_tc_kernel, dim3(grid), dim3(448), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
+               scale, scale * 1.4426950408889634f, dq_acc, g_attn_dq_direct, g_attn_kv_tmem, g_attn_dbg);
+  }
   const size_t n8 = rows * C / 8;
   launch_pdl(attn_dq_convert_kernel, dim3(static_cast<unsigned>((n8 + 255) / 256)), dim3(256), 0, stream, dq_acc, static_cast<__nv_bfloat16*>(dqkv), rows, C);
   count_launch(3);
