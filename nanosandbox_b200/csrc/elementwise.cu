@@ -252,8 +252,10 @@ __global__ void __launch_bounds__(256, 2)
 // (cp.async.bulk + mbarrier), 8 consumer warps take one row each from shared memory.  Memory latency is
 // hidden by the ring instead of by occupancy; each consumer only holds its dw/db partials in registers.
 constexpr int kLnRows = 8;
+constexpr int kLnGroups = 2;                         // consumer groups of kLnRows warps, taking alternate slabs
+constexpr int kLnWarps = kLnRows * kLnGroups;        // consumer warps (the producer is warp kLnWarps)
 template <int NV, typename DyT, bool HAS_DB>
-__global__ void __launch_bounds__(288, 1)
+__global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
     layernorm_bwd_stream_kernel(const DyT* __restrict__ dy, const float* __restrict__ x,
                                 const float* __restrict__ w, const float* __restrict__ mean,
                                 const float* __restrict__ rstd, const float* __restrict__ dres_in,
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(288, 1)
 #pragma unroll
   for (int j = 0; j < (HAS_DB ? NV : 1); ++j) dbacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
 
-  if (warp == kLnRows) {
+  if (warp == kLnWarps) {
     if (lane == 0) {
       int it = 0;
       for (int g = blockIdx.x; g < ngroups; g += gridDim.x, ++it) {
@@ -299,22 +301,30 @@ __global__ void __launch_bounds__(288, 1)
     }
   } else {
     const float invC = 1.0f / static_cast<float>(C);
+    // two groups of kLnRows warps take alternate slabs (four consumer warps per SM sub-partition hide the
+    // shared-memory and shuffle latencies of one another); every warp observes every slab's barrier so that
+    // the phases are seen in order, and processes / releases only its own group's slabs
+    const int cg = warp / kLnRows, wr = warp % kLnRows;   // consumer group, row within the slab
     int it = 0;
     int g = blockIdx.x;
     float mu_n = 0.f, rs_n = 0.f;
-    if (g < ngroups && g * kLnRows + warp < M) { mu_n = mean[g * kLnRows + warp]; rs_n = rstd[g * kLnRows + warp]; }
+    {
+      const int g0 = g + cg * gridDim.x;                  // this group's first slab
+      if (g0 < ngroups && g0 * kLnRows + wr < M) { mu_n = mean[g0 * kLnRows + wr]; rs_n = rstd[g0 * kLnRows + wr]; }
+    }
     for (; g < ngroups; g += gridDim.x, ++it) {
       const int s = it % nstages;
-      const int row = g * kLnRows + warp;
-      const float mu = mu_n, rs = rs_n;
-      const int gn = g + gridDim.x;                       // statistics of the next row, one iteration ahead
-      if (gn < ngroups && gn * kLnRows + warp < M) { mu_n = mean[gn * kLnRows + warp]; rs_n = rstd[gn * kLnRows + warp]; }
       ptx::mbar_wait(&full[s], (it / nstages) & 1);
+      if ((it % kLnGroups) != cg) continue;
+      const int row = g * kLnRows + wr;
+      const float mu = mu_n, rs = rs_n;
+      const int gn = g + kLnGroups * gridDim.x;           // statistics of this group's next slab, one turn ahead
+      if (gn < ngroups && gn * kLnRows + wr < M) { mu_n = mean[gn * kLnRows + wr]; rs_n = rstd[gn * kLnRows + wr]; }
       if (row < M) {
         const uint8_t* st = ln_smem + static_cast<size_t>(s) * stage_bytes;
-        const DyT* sdy = reinterpret_cast<const DyT*>(st) + warp * C;
-        const float* sx = reinterpret_cast<const float*>(st + off_x) + warp * C;
-        const float* sr = reinterpret_cast<const float*>(st + off_r) + warp * C;
+        const DyT* sdy = reinterpret_cast<const DyT*>(st) + wr * C;
+        const float* sx = reinterpret_cast<const float*>(st + off_x) + wr * C;
+        const float* sr = reinterpret_cast<const float*>(st + off_r) + wr * C;
         const size_t off = static_cast<size_t>(row) * C;
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
@@ -363,7 +373,7 @@ __global__ void __launch_bounds__(288, 1)
 #pragma unroll
   for (int pass = 0; pass < (HAS_DB ? 2 : 1); ++pass) {
     if (pass > 0) __syncthreads();
-    if (warp < kLnRows) {
+    if (warp < kLnWarps) {
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
         const int c = (lane + 32 * j) * 4;
@@ -375,7 +385,7 @@ __global__ void __launch_bounds__(288, 1)
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       float s = 0.f;
 #pragma unroll
-      for (int k = 0; k < kLnRows; ++k) s += red[k * 128 * NV + c];
+      for (int k = 0; k < kLnWarps; ++k) s += red[k * 128 * NV + c];
       part[(static_cast<size_t>(blockIdx.x) * 2 + pass) * C + c] = s;
     }
   }
@@ -1081,7 +1091,7 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
   int nstages = static_cast<int>((200 * 1024) / slab);
   if (nstages > 4) nstages = 4;
   const bool stream_ok = (dy_row % 16 == 0) && (C % 4 == 0) && nstages >= 2 && M >= 4 * kLnRows &&
-                         static_cast<size_t>(nstages) * slab >= static_cast<size_t>(kLnRows) * 128 * nv * 4;
+                         static_cast<size_t>(nstages) * slab >= static_cast<size_t>(kLnWarps) * 128 * nv * 4;
   if (stream_ok) {
     int sgrid = (M + kLnRows - 1) / kLnRows;
     if (sgrid > sm_count()) sgrid = sm_count();
@@ -1092,7 +1102,7 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
   {                                                                                                     \
     auto kern = layernorm_bwd_stream_kernel<NV, TT, HASDB>;                                             \
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 210 * 1024);                \
-    launch_pdl(kern, dim3(grid), dim3(288), smem, stream, static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx,        \
+    launch_pdl(kern, dim3(grid), dim3(32 * (kLnWarps + 1)), smem, stream, static_cast<const TT*>(dy), x, w, mean, rstd, dres_in, dx,        \
                                        static_cast<__nv_bfloat16*>(dx_lowp), scratch, M, C, nstages);   \
   }
     NSB_LN_DISPATCH(nv, {
