@@ -350,7 +350,282 @@ __global__ void __launch_bounds__(192, 2)
   }
 }
 
+// ---- forward with eight softmax warps per CTA (four per SM sub-partition with two CTAs per SM) -------
+// Same pipeline as attn_fwd_tc_kernel; each query row is shared by two threads (64 key columns each), P always
+// lives in tensor memory, 80 registers per thread.  Warps: 0 TMA, 1 MMA issue, 2..9 softmax.
+__global__ void __launch_bounds__(320, 2)
+    attn_fwd_tc8_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ y,
+                       float* __restrict__ lse, int Tn, int H, float scale_log2) {
+  constexpr int p_in_tmem = 1;
+  long long* const dbg = nullptr;
+  using namespace fatc;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sQ = smem;
+  uint8_t* sKV = smem + TILE;                       // stage s: K at s*2*TILE, V at s*2*TILE + TILE
+  uint8_t* sP = sKV + KV_STAGES * 2 * TILE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + P_BYTES);
+  uint64_t* q_full = bars;
+  uint64_t* kv_full = bars + 1;                     // [2]
+  uint64_t* kv_empty = bars + 3;                    // [2]
+  uint64_t* s_full = bars + 5;
+  uint64_t* p_full = bars + 6;
+  uint64_t* o_full = bars + 7;
+  uint64_t* pv_done = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int C = H * HD;
+  const int qb = gridDim.y - 1 - blockIdx.y;        // longest query blocks of ALL heads are scheduled first
+  const int bh = blockIdx.x, b = bh / H, h = bh % H;
+  const int q0 = qb * BQ;
+  const int nblk = qb + 1;                          // causal: key blocks 0..qb
+  const int row_base = b * Tn;                      // row of token 0 of this batch in [B*T, 3C]
+
+  if (dbg != nullptr && threadIdx.x == 0) {         // per-CTA trace: start ns, end ns, SM id
+    unsigned long long t; unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    long long* rec3 = dbg + 1024 + 3 * (blockIdx.y * gridDim.x + blockIdx.x);
+    rec3[0] = static_cast<long long>(t);
+    rec3[2] = smid;
+  }
+  if (threadIdx.x == 0) {
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+    ptx::prefetch_tmap(&tmap_qkv);
+  }
+  if (warp == 0 && lane < 9) {                       // one barrier per lane: q_full, kv_full[2], kv_empty[2], s_full, p_full, o_full, pv_done
+    static_assert(KV_STAGES == 2, "barrier layout");
+    ptx::mbar_init(&bars[lane], lane == 6 ? 8u : 1u);   // p_full collects the eight softmax warps
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  // barriers, TMEM and the descriptor prefetch above overlap the previous kernel's tail
+  pdl_wait();     // dependent launch: the previous kernel has completed beyond this point
+  pdl_trigger();  // ... and the next one may be scheduled as our CTAs retire
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(q_full, TILE);
+      ptx::tma_load_2d(sQ, &tmap_qkv, q_full, h * HD, row_base + q0);
+      for (int j = 0; j < nblk; ++j) {
+        const int s = j % KV_STAGES;
+        ptx::mbar_wait(&kv_empty[s], ((j / KV_STAGES) & 1) ^ 1);
+        ptx::mbar_expect_tx(&kv_full[s], 2 * TILE);
+        ptx::tma_load_2d(sKV + s * 2 * TILE, &tmap_qkv, &kv_full[s], C + h * HD, row_base + j * BKV);
+        ptx::tma_load_2d(sKV + s * 2 * TILE + TILE, &tmap_qkv, &kv_full[s], 2 * C + h * HD, row_base + j * BKV);
+      }
+    }
+  } else if (warp == 1) {
+    // MMA issuer: the warp stays converged, one elected lane issues (see ptx::elect_one)
+    {
+      constexpr uint32_t IDESC_S = ptx::umma_idesc_bf16(BQ, BKV, false, false);
+      constexpr uint32_t IDESC_O = ptx::umma_idesc_bf16(BQ, HD, false, true);   // B = V, MN-major
+      const bool rec = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+      // descriptors: only the 14-bit start-address field changes between MMAs
+      const uint64_t q_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(sQ), 16, 1024);
+      const uint64_t p_desc0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(sP), 16, 1024);
+      const uint64_t k_desc0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(sKV), 16, 1024);
+      const uint64_t v_desc0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(sKV + TILE), 64 * BKV * 2, 1024);
+      auto issue_s = [&](int jj) {                 // S = Q K_jj^T
+        const uint64_t k_desc = k_desc0 + static_cast<uint64_t>(((jj % KV_STAGES) * 2 * TILE) >> 4);
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k)
+            ptx::umma_bf16(tmem + S_COL, q_desc + static_cast<uint64_t>(2 * k), k_desc + static_cast<uint64_t>(2 * k),
+                           IDESC_S, k > 0 ? 1u : 0u);
+          ptx::umma_commit(s_full);
+        }
+        __syncwarp();
+      };
+      ptx::mbar_wait(q_full, 0);
+      ptx::mbar_wait(&kv_full[0], 0);
+      ptx::tc_fence_after();
+      issue_s(0);
+      for (int j = 0; j < nblk; ++j) {
+        const int s = j % KV_STAGES;
+        if (rec) dbg[512 + 4 * j] = clock64();
+        ptx::mbar_wait(p_full, j & 1);              // P_j in smem, S consumed, O rescaled if needed
+        ptx::tc_fence_after();
+        if (rec) dbg[512 + 4 * j + 1] = clock64();
+        if (j + 1 < nblk) {                         // next S first: the softmax warps wait for it
+          ptx::mbar_wait(&kv_full[(j + 1) % KV_STAGES], ((j + 1) / KV_STAGES) & 1);
+          ptx::tc_fence_after();
+          issue_s(j + 1);
+        }
+        if (rec) dbg[512 + 4 * j + 2] = clock64();
+        // O += P_j V_j.  P: K-major, two 64-column atoms of 16 KB; V: MN-major, 16 key rows = 2048 B / step
+        const uint64_t v_desc = v_desc0 + static_cast<uint64_t>((s * 2 * TILE) >> 4);
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int k = 0; k < BKV / 16; ++k)
+            if (p_in_tmem) ptx::umma_bf16_ts(tmem + O_COL, tmem + P_COL + 8 * k, v_desc + static_cast<uint64_t>(128 * k), IDESC_O,
+                                             (j > 0 || k > 0) ? 1u : 0u);
+            else ptx::umma_bf16(tmem + O_COL, p_desc0 + static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4),
+                                v_desc + static_cast<uint64_t>(128 * k), IDESC_O, (j > 0 || k > 0) ? 1u : 0u);
+          ptx::umma_commit(pv_done);                // P smem may be overwritten
+          ptx::umma_commit(&kv_empty[s]);           // K/V stage may be refilled
+          if (j == nblk - 1) ptx::umma_commit(o_full);
+        }
+        __syncwarp();
+        if (rec) dbg[512 + 4 * j + 3] = clock64();
+      }
+    }
+  } else {
+    // ---- eight softmax warps: group g takes key columns 64 g .. 64 g + 63 of every block; the two threads of a
+    //      query row (same lane, warps w and w + 4) keep the same exponent reference m and exchange their
+    //      row maxima once per block through shared memory; each keeps the sum of its own columns ----
+    const int g = (warp - 2) >> 2;
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;                 // query row within the tile = TMEM lane
+    const int rq = row >> 5;
+    const int qi = q0 + row;
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    float m = -INFINITY, l = 0.f;
+    const uint32_t s_addr = tmem + lane_addr + S_COL + g * 64;
+    const uint32_t o_addr = tmem + lane_addr + O_COL + g * 32;   // this thread's half of the O row
+    const uint32_t p_addr = tmem + lane_addr + P_COL + g * 32;   // its 64 probabilities as 32 bf16 pairs
+    float* xch = reinterpret_cast<float*>(sP);      // [2 buffers][2 groups][128 rows] maxima, then [2][128] sums
+    for (int j = 0; j < nblk; ++j) {
+      ptx::mbar_wait(s_full, j & 1);
+      ptx::tc_fence_after();
+      const bool diag = (j == qb);
+      bool p_free = (j == 0);                       // P of the previous block still being read by its P V?
+      // one pass over this thread's 64 columns with the current m: P -> tensor memory, returns the sum of P
+      // and (mx) the raw maximum.  Diagonal block: per 32 x 32 sub-block all valid / masked per element / zeros.
+      auto pass = [&](float& mx) -> float {
+        float s0 = 0.f, s1 = 0.f;
+        mx = -INFINITY;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          const int cc = g * 2 + c;
+          uint32_t pw[16];
+          if (diag && cc > rq) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) pw[i] = 0u;
+          } else {
+            float cur[32];
+            ptx::tmem_ld_32x32(s_addr + c * 32, cur);
+            if (diag && cc == rq) {
+              const int lim = row - cc * 32;        // last valid column of this chunk
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                if (i <= lim) mx = fmaxf(mx, cur[i]);
+                float p = fatc::ex2(fmaf(cur[i], scale_log2, -m));
+                if (i > lim) p = 0.f;
+                cur[i] = p;
+                if (i & 1) s1 += p; else s0 += p;
+              }
+            } else {
+              const f32x2 sc2 = pack2(scale_log2, scale_log2), nm2 = pack2(-m, -m);
+              f32x2 acc = pack2(s0, s1);
+#pragma unroll
+              for (int i = 0; i < 32; i += 2) {
+                mx = max3(mx, cur[i], cur[i + 1]);
+                float a0, a1;
+                unpack2(fma2(pack2(cur[i], cur[i + 1]), sc2, nm2), a0, a1);
+                cur[i] = fatc::ex2(a0);
+                cur[i + 1] = fatc::ex2(a1);
+                acc = add2(acc, pack2(cur[i], cur[i + 1]));
+              }
+              unpack2(acc, s0, s1);
+            }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) pw[i] = pack_bf16x2(cur[2 * i], cur[2 * i + 1]);
+          }
+          if (!p_free) { ptx::mbar_wait(pv_done, (j - 1) & 1); ptx::tc_fence_after(); p_free = true; }
+          ptx::tmem_st_32x16_u32_nowait(p_addr + c * 16, pw);
+        }
+        ptx::tmem_wait_st();
+        return s0 + s1;
+      };
+      float mx, sum = 0.f;
+      if (j == 0) {
+        // first block: only the maximum (m = -inf would make every P infinite)
+        mx = -INFINITY;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          const int cc = g * 2 + c;
+          if (diag && cc > rq) continue;            // warp-uniform
+          float v[32];
+          ptx::tmem_ld_32x32(s_addr + c * 32, v);
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (!diag || cc * 32 + i <= row) mx = fmaxf(mx, v[i]);
+        }
+      } else {
+        sum = pass(mx);
+      }
+      // row maximum over both halves (double-buffered slots: the partner reads this block's value while I may
+      // already be writing the next block's)
+      float* slot = xch + (j & 1) * 256;
+      slot[g * 128 + row] = mx;
+      ptx::named_bar_sync(2, 256);
+      mx = fmaxf(mx, slot[(g ^ 1) * 128 + row]);
+      float corr = 1.f;
+      const float m_true = mx * scale_log2;
+      const bool grow = m_true > m + 8.f;
+      if (__any_sync(0xffffffffu, grow)) {           // same decision in both warps of these 32 rows
+        if (grow) {
+          corr = fatc::ex2(m - m_true);              // first block: exp2(-inf) = 0
+          l *= corr;
+          m = m_true;
+        }
+        float dummy;
+        sum = pass(dummy);
+      }
+      l += sum;
+      if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+        // rare: rescale this thread's half of the O row in tensor memory
+        float v[32];
+        ptx::tmem_ld_32x32(o_addr, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] *= corr;
+        ptx::tmem_st_32x32(o_addr, v);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(p_full);
+    }
+    // total row sum, then this thread's 32 columns of O
+    float* lsum = xch + 512;
+    lsum[g * 128 + row] = l;
+    ptx::named_bar_sync(2, 256);
+    l += lsum[(g ^ 1) * 128 + row];
+    ptx::mbar_wait(o_full, 0);
+    ptx::tc_fence_after();
+    {
+      const float inv = 1.f / l;
+      const bool live = qi < Tn;                     // TMEM loads stay warp-collective; stores are predicated
+      uint4* dst = reinterpret_cast<uint4*>(y + (static_cast<size_t>(row_base) + (live ? qi : 0)) * C + h * HD + g * 32);
+      float o[32];
+      ptx::tmem_ld_32x32(o_addr, o);
+      if (live) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          dst[i] = make_uint4(pack_bf16x2(o[8 * i] * inv, o[8 * i + 1] * inv), pack_bf16x2(o[8 * i + 2] * inv, o[8 * i + 3] * inv),
+                              pack_bf16x2(o[8 * i + 4] * inv, o[8 * i + 5] * inv), pack_bf16x2(o[8 * i + 6] * inv, o[8 * i + 7] * inv));
+        if (g == 0) lse[(static_cast<size_t>(b) * H + h) * Tn + qi] = (m + log2f(l)) * 0.69314718055994531f;
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem, TMEM_COLS);
+  if (dbg != nullptr && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    dbg[1024 + 3 * (blockIdx.y * gridDim.x + blockIdx.x) + 1] = static_cast<long long>(t);
+  }
+}
+
+
 static long long* g_attn_dbg = nullptr;
+static int g_attn_fwd_warps8 = 1;  // forward with eight softmax warps per CTA (attn_fwd_tc8_kernel); 0: the four-warp kernel
+void attention_tc_set_fwd_warps8(int on) { g_attn_fwd_warps8 = on; }
 static int g_attn_fwd_p_tmem = 1;  // forward: P kept in tensor memory for the P V MMA (0: through shared memory)
 void attention_tc_set_fwd_p_tmem(int on) { g_attn_fwd_p_tmem = on; }
 void attention_tc_set_debug_buffer(long long* p) { g_attn_dbg = p; }
@@ -377,8 +652,19 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
     attr_done = true;
   }
   const dim3 grid(B * H, (T + BQ - 1) / BQ);
-  launch_pdl(attn_fwd_tc_kernel, dim3(grid), dim3(192), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
-                                                        1.4426950408889634f / sqrtf(static_cast<float>(HD)), g_attn_fwd_p_tmem, g_attn_dbg);
+  if (g_attn_fwd_warps8 && g_attn_dbg == nullptr) {
+    static bool attr8 = false;
+    if (!attr8) {
+      cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+      NSB_REQUIRE(e == cudaSuccess, "attention_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      attr8 = true;
+    }
+    launch_pdl(attn_fwd_tc8_kernel, dim3(grid), dim3(320), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
+               1.4426950408889634f / sqrtf(static_cast<float>(HD)));
+  } else {
+    launch_pdl(attn_fwd_tc_kernel, dim3(grid), dim3(192), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
+               1.4426950408889634f / sqrtf(static_cast<float>(HD)), g_attn_fwd_p_tmem, g_attn_dbg);
+  }
   count_launch();
   return check_launch("attention_fwd_tc");
 }

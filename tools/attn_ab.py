@@ -17,11 +17,10 @@ def t(fn, n=20):
 for _ in range(2):
     print(f"attention fwd {t(lambda: ops.attention_fwd(qkv, y, lse, B, T, H, D)):.1f} us   bwd (3 kernels) {t(lambda: ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc)):.1f} us")
 lib = _lib.load()
-ops.attention_fwd(qkv, y, lse, B, T, H, D)
 outs = {}
-for mode in (12, 13, 12, 13):
+for mode in (14, 15, 14, 15):
     lib.nsb_attention_debug_config(mode)
-    us = t(lambda: ops.attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc))
-    print("backward,", "8 probability warps" if mode == 12 else "16 probability warps", f"{us:.1f} us")
-    outs[mode] = dqkv.float().clone()
-print("max |diff| between the two forms:", (outs[12] - outs[13]).abs().max().item(), " ref max", outs[12].abs().max().item())
+    us = t(lambda: ops.attention_fwd(qkv, y, lse, B, T, H, D))
+    print("forward,", "4 softmax warps" if mode == 14 else "8 softmax warps", f"{us:.1f} us")
+    outs[mode] = (y.float().clone(), lse.clone())
+print("max |diff| y:", (outs[14][0] - outs[15][0]).abs().max().item(), " lse:", (outs[14][1] - outs[15][1]).abs().max().item(), " y max", outs[14][0].abs().max().item())
