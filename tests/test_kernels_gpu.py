@@ -391,6 +391,26 @@ def test_attention_bf16_paths(path, B, T, H):
         lib.nsb_attention_debug_config(0)
 
 
+@pytest.mark.parametrize("mode", [12, 14, 5, 6, 10])
+@pytest.mark.parametrize("B,T,H", [(2, 256, 3), (1, 1000, 2)])
+def test_attention_tc_kernel_variants(mode, B, T, H):
+    """The earlier forms of the tcgen05 kernels stay selectable for A/B runs (8 probability warps backward: 12,
+    4 softmax warps forward: 14, every A operand from shared memory: 5, K/V from tensor memory: 6, forward P
+    through shared memory: 10; the 4-warp forward is the one modes 10 / 11 act on): each must pass the same
+    parity check as the defaults."""
+    lib = _lib.load()
+    if mode in (5, 6):
+        lib.nsb_attention_debug_config(12)      # these two switches act on the 8-warp backward kernel
+    if mode == 10:
+        lib.nsb_attention_debug_config(14)
+    lib.nsb_attention_debug_config(mode)
+    try:
+        test_attention_fwd_bwd(torch.bfloat16, B, T, H, 64)
+    finally:
+        for m in (13, 15, 9, 11):               # back to the defaults
+            lib.nsb_attention_debug_config(m)
+
+
 @pytest.mark.parametrize("dt,B,T,H,D", [
     (torch.float32, 2, 64, 4, 32), (torch.float32, 2, 100, 2, 64),
     (torch.bfloat16, 2, 256, 6, 64), (torch.bfloat16, 1, 1024, 2, 64), (torch.bfloat16, 3, 100, 2, 64),

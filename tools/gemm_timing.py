@@ -20,7 +20,8 @@ dbg = torch.zeros(8192, dtype=torch.int64, device="cuda")
 f = lambda: ops.gemm(M, N, K, A, K if a_k else M, bool(a_k), B, K if b_k else N, bool(b_k), C, N, epi,
                      C2=C2 if epi == E.EPI_GELU else None, aux=aux)
 import os
-if os.environ.get("GEMM_MODE"): lib.nsb_gemm_debug_config(0, 0, int(os.environ["GEMM_MODE"]))
+if os.environ.get("GEMM_BN"): lib.nsb_gemm_debug_config(int(os.environ["GEMM_BN"]), 0, int(os.environ.get("GEMM_MODE", "0")))
+elif os.environ.get("GEMM_MODE"): lib.nsb_gemm_debug_config(0, 0, int(os.environ["GEMM_MODE"]))
 if os.environ.get("GEMM_PIPE"): lib.nsb_gemm_debug_pipeline(*[int(x) for x in os.environ["GEMM_PIPE"].split(",")])
 f(); f()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
