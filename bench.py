@@ -26,20 +26,46 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-CFG = dict(n_layer=12, n_head=12, n_embd=768, block_size=1024, vocab_size=50304, bias=False, dropout=0.0)
-BATCH, ACCUM_TOTAL = 12, 40
-WORKLOAD = "gpt2-124M (12L/12H/768, block 1024, vocab 50304) batch 12 x accum 40 = 491520 tokens/step, bf16 [BASELINE.json configs[3]]"
-FLOPS_PER_TOKEN = 854_770_176  # 6N + 12LHQT, SURVEY.md 8d
+# BASELINE.json configs -> bench workloads.  "gpt2" (configs[3]) is the one the metric is quoted on and the default;
+# "char" is configs[1] at N=1 and configs[2] at N=8 (one 64x256 micro-step per rank, gradient_accumulation_steps =
+# world size, as the reference launches it); "gpt2-medium" is configs[4]'s model (its 8-Pod launch form is
+# tools/multipod_emulation.sh; under plain torchrun this measures the same step single-Pod).
+WORKLOADS = {
+    "gpt2": dict(cfg=dict(n_layer=12, n_head=12, n_embd=768, block_size=1024, vocab_size=50304, bias=False, dropout=0.0),
+                 batch=12, accum_total=40, scaling="strong", cpu_micro_batch=2,
+                 label="gpt2-124M (12L/12H/768, block 1024, vocab 50304) batch 12 x accum 40 = 491520 tokens/step, bf16 [BASELINE.json configs[3]]"),
+    "char": dict(cfg=dict(n_layer=6, n_head=6, n_embd=384, block_size=256, vocab_size=65, bias=False, dropout=0.0),
+                 batch=64, accum_total=None, scaling="weak", cpu_micro_batch=64,
+                 label="shakespeare_char GPT (6L/6H/384, block 256, vocab 65) batch 64, one micro-step per rank "
+                       "(gradient_accumulation_steps = world size), bf16 [BASELINE.json configs[1] at N=1, configs[2] at N=8]"),
+    "gpt2-medium": dict(cfg=dict(n_layer=24, n_head=16, n_embd=1024, block_size=1024, vocab_size=50304, bias=False, dropout=0.0),
+                        batch=12, accum_total=40, scaling="strong", cpu_micro_batch=1,
+                        label="gpt2-medium 350M (24L/16H/1024, block 1024, vocab 50304) batch 12 x accum 40 = 491520 tokens/step, bf16 [BASELINE.json configs[4] model]"),
+}
 NOMINAL_BF16 = 2.25e15
 
 
-def gemm_traffic_bytes():
-    """dram bytes per GEMM launch from the committed ncu capture of this workload (profiles/), or None."""
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01d_gemm_traffic.json")) as f:
-            return float(json.load(f)["dram_bytes_per_launch"])
-    except (OSError, KeyError, ValueError):
-        return None
+def flops_per_token(cfg) -> int:
+    """nanoGPT's estimate_mfu numerator per token: 6N + 12*L*H*Q*T, N = parameters without wpe."""
+    L, H, C, T, V = cfg["n_layer"], cfg["n_head"], cfg["n_embd"], cfg["block_size"], cfg["vocab_size"]
+    per_block = 12 * C * C + 2 * C + (13 * C if cfg["bias"] else 0)
+    n = V * C + L * per_block + C + (C if cfg["bias"] else 0)
+    return 6 * n + 12 * L * H * (C // H) * T
+
+
+def gemm_traffic_bytes(workload: str):
+    """(dram bytes per GEMM launch, where the figure comes from).  ncu cannot run inside a timed bench, so the
+    figure is the one of the committed `ncu --set full` capture of this same workload under profiles/ (newest
+    first); None for workloads without a capture."""
+    if workload != "gpt2":
+        return None, None
+    for name in ("r02_gemm_traffic.json", "r01d_gemm_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                return float(json.load(f)["dram_bytes_per_launch"]), f"profiles/{name} (ncu capture of this workload, not measured in this run)"
+        except (OSError, KeyError, ValueError):
+            continue
+    return None, None
 
 
 def load_peaks():
@@ -83,47 +109,61 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_reference_run(steps: int, warmup: int, micro_batch: int = 2):
-    """The reference's CPU path (oracle restatement, stock torch ops) on all host cores, on a
-    bounded sample of the workload: one micro-step of `micro_batch` x 1024 tokens per step."""
+def cpu_reference_run(wl, world: int, n_micro: int, warmup: int):
+    """The reference's CPU path (oracle restatement, stock torch ops) on all host cores, on a bounded sample of
+    the workload.  A full optimizer step is `k` forward+backward micro-steps followed by ONE clip + AdamW, so
+    the two parts are timed separately on the sample (`n_micro` micro-steps of `cpu_micro_batch` sequences, two
+    optimizer updates) and composed: step time = (tokens per step / tokens per micro-step) * t_micro + t_opt."""
     from oracle.model import GPT as RefGPT, GPTConfig as RefConfig
+    cfg = wl["cfg"]
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     torch.manual_seed(1337)
-    model = RefGPT(RefConfig(**CFG), verbose=False)
+    model = RefGPT(RefConfig(**cfg), verbose=False)
     opt = model.configure_optimizers(0.1, 6e-4, (0.9, 0.95), "cpu", verbose=False)
     g = torch.Generator().manual_seed(0)
-    toks = torch.randint(0, CFG["vocab_size"], (1 << 20,), generator=g)
-    T = CFG["block_size"]
+    toks = torch.randint(0, cfg["vocab_size"], (1 << 20,), generator=g)
+    T, mb = cfg["block_size"], wl["cpu_micro_batch"]
+    accum_total = wl["accum_total"] or world
+    tokens_per_step = accum_total * wl["batch"] * T
 
-    def one():
-        ix = torch.randint(len(toks) - T - 1, (micro_batch,))
+    def micro():
+        ix = torch.randint(len(toks) - T - 1, (mb,))
         x = torch.stack([toks[i:i + T] for i in ix])
         y = torch.stack([toks[i + 1:i + 1 + T] for i in ix])
         _, loss = model(x, y)
         loss.backward()
+
+    def update():
         torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
         opt.step()
         opt.zero_grad(set_to_none=True)
-        return float(loss.detach())
 
-    for _ in range(warmup):
-        one()
+    for _ in range(max(1, warmup)):
+        micro()
+    update()                                   # warm (allocates the AdamW state)
     t0 = time.perf_counter()
-    for _ in range(steps):
-        one()
-    dt = time.perf_counter() - t0
-    tok_s = steps * micro_batch * T / dt
-    sample = (f"{steps} optimizer steps of one {micro_batch}x{T}-token micro-step (fwd+bwd+clip+AdamW), fp32, "
-              f"oracle/ restatement on stock torch CPU ops, {cores} threads; the full step is 240x this sample")
-    return tok_s, dt / steps * 1e3, cores, sample
+    for _ in range(n_micro):
+        micro()
+    t_micro = (time.perf_counter() - t0) / n_micro
+    t0 = time.perf_counter()
+    update()
+    t_opt = time.perf_counter() - t0
+    k = tokens_per_step / (mb * T)
+    step_s = k * t_micro + t_opt
+    sample = (f"{n_micro} forward+backward micro-steps of {mb}x{T} tokens ({t_micro * 1e3:.0f} ms each) and one clip+AdamW "
+              f"update ({t_opt * 1e3:.0f} ms), fp32, oracle/ restatement on stock torch CPU ops, {cores} threads; composed "
+              f"as {k:.0f} micro-steps + 1 update per {tokens_per_step}-token optimizer step")
+    return tokens_per_step / step_s, step_s * 1e3, cores, sample
 
 
-def torch_gpu_baseline(dev, micro_steps: int = 8):
+def torch_gpu_baseline(dev, wl, micro_steps: int = 8):
     """Informational: the SAME step on stock PyTorch CUDA ops (oracle model under bf16 autocast,
     SDPA flash attention, cuBLAS, fused AdamW) on this GPU, for `micro_steps` micro-steps."""
     from oracle.model import GPT as RefGPT, GPTConfig as RefConfig
     torch.manual_seed(1337)
+    CFG, BATCH = wl["cfg"], wl["batch"]
+    micro_steps = min(micro_steps, wl["accum_total"] or 1)
     model = RefGPT(RefConfig(**CFG), verbose=False).to(dev)
     opt = model.configure_optimizers(0.1, 6e-4, (0.9, 0.95), "cuda", verbose=False)
     T, V = CFG["block_size"], CFG["vocab_size"]
@@ -160,13 +200,15 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 3))
+    wl = WORKLOADS[args.config]
+    world = max(1, args.gpus)
+    n_micro = max(1, min(args.steps, 6))
     warm = 1 if args.warmup > 0 else 0
-    tok_s, ms, cores, sample = cpu_reference_run(steps, warm)
+    tok_s, ms, cores, sample = cpu_reference_run(wl, world, n_micro, warm)
     line = {"impl": "reference", "metric": "train_tokens_per_sec", "value": tok_s, "unit": "tokens/s",
-            "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD},
+            "n_gpus": args.gpus, "steps": n_micro, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": wl["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["label"]},
             "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": tok_s, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
@@ -198,6 +240,8 @@ def main():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="gpt2", choices=sorted(WORKLOADS),
+                    help="BASELINE.json workload; the default (gpt2 = configs[3]) is the headline line")
     ap.add_argument("--bucket-dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-torch-baseline", action="store_true")
@@ -226,10 +270,14 @@ def main():
     ddp = world > 1
     if ddp:
         dist.init_process_group(backend="nccl", device_id=dev)
-    assert ACCUM_TOTAL % world == 0
-    accum = ACCUM_TOTAL // world
+    wl = WORKLOADS[args.config]
+    CFG, BATCH = wl["cfg"], wl["batch"]
+    accum_total = wl["accum_total"] or world           # "char": one micro-step per rank
+    assert accum_total % world == 0, f"{accum_total} micro-steps do not split over {world} ranks"
+    accum = accum_total // world
     T, V = CFG["block_size"], CFG["vocab_size"]
-    tokens_per_step = ACCUM_TOTAL * BATCH * T
+    tokens_per_step = accum_total * BATCH * T
+    FLOPS_PER_TOKEN = flops_per_token(CFG)
 
     torch.manual_seed(1337 + rank)
     model = GPT(GPTConfig(**CFG), verbose=False).to(dev)
@@ -246,12 +294,12 @@ def main():
         y = torch.stack([torch.from_numpy(data[i + 1:i + 1 + T].astype(np.int64)) for i in ix])
         return x.pin_memory(), y.pin_memory()
 
-    def train_step(batches, from_host: bool):
+    def train_step(batches, from_host: bool, sync: bool = True, update: bool = True):
         """One optimizer step through the public API (GPT.forward / backward / clip / AdamW)."""
         loss = None
         for micro in range(accum):
             if ddp:
-                model.require_backward_grad_sync = (micro == accum - 1)
+                model.require_backward_grad_sync = sync and (micro == accum - 1)
             if from_host:
                 xh, yh = host_batch()
                 X, Y = xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)
@@ -261,9 +309,10 @@ def main():
                 _, loss = model(X, Y)
                 loss = loss / accum
             loss.backward()
-        opt.clip_grad_norm_(1.0)
-        opt.step()
-        opt.zero_grad(set_to_none=True)
+        if update:
+            opt.clip_grad_norm_(1.0)
+            opt.step()
+            opt.zero_grad(set_to_none=True)
         return loss
 
     resident = [tuple(t.to(dev) for t in host_batch()) for _ in range(accum)]
@@ -286,8 +335,13 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms.item()
 
-    # ---- warm-up, then the device-resident timed region ("value") ----
-    for _ in range(args.warmup):
+    # ---- warm-up (the first step doubles as the sanity check: a random-init model must sit at ln V), then the
+    #      device-resident timed region ("value") ----
+    loss0 = train_step(resident, False).item() * accum
+    if not abs(loss0 - math.log(V)) < 0.2:
+        raise SystemExit(f"bench.py: loss at init {loss0:.4f} is not within 0.2 of ln({V}) = {math.log(V):.4f}: "
+                         "the step is not computing the model")
+    for _ in range(args.warmup - 1):
         train_step(resident, False)
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -345,44 +399,90 @@ def main():
     achieved = g_flops / (g_ms / 1e3) / 1e12
     roofline = {"kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA bf16 GEMM, all layouts/epilogues)", "bound": "tensor",
                 "achieved": achieved, "peak": peaks["tf_sus"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sus"],
-                "traffic": gemm_traffic_bytes(), "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json bf16_tflops_sustained: kernel timed inside a long step)",
+                "traffic": gemm_traffic_bytes(args.config)[0], "traffic_source": gemm_traffic_bytes(args.config)[1],
+                "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json bf16_tflops_sustained: kernel timed inside a long step)",
                 "launches_timed": len(ev), "avg_launch_us": g_ms * 1e3 / max(1, len(ev)),
                 "algorithmic_flops_per_launch": g_flops / max(1, len(ev)),
                 "gemm_share_of_step": g_ms / (ms / args.steps)}
 
-    # ---- all-reduce bus bandwidth (N > 1): events on the communication stream ----
+    # ---- data-parallel path (N > 1): correctness check, exposed communication, bus bandwidth ----
     comm = None
+    ddp_check = None
     if ddp:
-        model.buckets.time_comm = True
-        model.buckets.comm_events = []
-        b0 = model.buckets.bytes_reduced
+        bk = model.buckets
+        # (1) replicas: every rank's parameter arena must be bit-identical to rank 0's after the timed steps
+        ar = raw.arena()
+        ref_params = ar.params.clone()
+        dist.broadcast(ref_params, src=0)
+        same = torch.tensor([int(torch.equal(ref_params, ar.params))], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        del ref_params
+        # (2) one step's synchronised gradients against all_reduce(locally accumulated gradients) / world
+        opt.zero_grad(set_to_none=True)
+        train_step(resident, False, sync=False, update=False)
+        expect = ar.grads.clone()
+        dist.all_reduce(expect, op=dist.ReduceOp.SUM)
+        expect /= world
+        opt.zero_grad(set_to_none=True)
+        train_step(resident, False, sync=True, update=False)
+        torch.cuda.synchronize()
+        gerr = ((ar.grads - expect).norm() / (expect.norm() + 1e-30)).reshape(1)
+        dist.all_reduce(gerr, op=dist.ReduceOp.MAX)
+        gtol = 1e-2 if args.bucket_dtype == "bf16" else 1e-5      # bf16 payload: 8 mantissa bits per addend
+        del expect
+        opt.zero_grad(set_to_none=True)
+        ddp_check = {"params_bit_equal_across_ranks": bool(same.item()), "synced_grad_rel_err": gerr.item(),
+                     "tolerance": gtol, "loss_at_init": loss0, "ln_vocab": math.log(V),
+                     "ok": bool(same.item()) and gerr.item() < gtol}
+        if not ddp_check["ok"]:
+            raise SystemExit(f"bench.py: data-parallel check failed: {ddp_check}")
+
+        # (3) time on the communication stream (pack + all-reduce + unpack, waiting included) and the
+        #     stand-alone bus bandwidth of the same payload
+        bk.time_comm = True
+        bk.comm_events = []
+        b0 = bk.bytes_reduced
         train_step(resident, False)
         torch.cuda.synchronize()
-        t_ms = sum(a.elapsed_time(b) for a, b in model.buckets.comm_events)
-        nbytes = model.buckets.bytes_reduced - b0
+        t_ms = sum(a.elapsed_time(b) for a, b in bk.comm_events)
+        nbytes = bk.bytes_reduced - b0
+        bk.time_comm = False
         t = torch.tensor([t_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        # stand-alone bus bandwidth of the same payload (one all-reduce over the whole bf16 staging arena)
-        stg = model.buckets.staging if model.buckets.staging is not None else model.buckets.grads
+        stg = bk.staging if bk.staging is not None else bk.grads
         for _ in range(2):
-            dist.all_reduce(stg)
+            bk.all_reduce(stg)
         torch.cuda.synchronize()
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a0.record()
         for _ in range(5):
-            dist.all_reduce(stg)
+            bk.all_reduce(stg)
         a1.record()
         torch.cuda.synchronize()
         alone = torch.tensor([a0.elapsed_time(a1) / 5], device=dev)
         dist.all_reduce(alone, op=dist.ReduceOp.MAX)
         sbytes = stg.numel() * stg.element_size()
+        # (4) exposed communication: step time minus the time of the same step with the collective
+        #     stubbed out (pack / unpack kernels still run), and minus the step with no gradient sync at all.
+        #     Last, because the replicas drift apart once their gradients are no longer averaged.
+        bk.stub_collective = True
+        train_step(resident, False)
+        ms_stub = timed(lambda: train_step(resident, False), args.steps)
+        bk.stub_collective = False
+        train_step(resident, False, sync=False)
+        ms_nosync = timed(lambda: train_step(resident, False, sync=False), args.steps)
+        step_ms = ms / args.steps
         comm = {"bytes_per_rank_per_step": nbytes, "ms_on_comm_stream": t.item(),
                 "standalone_ms": alone.item(),
                 "standalone_busbw_GBps": sbytes * 2 * (world - 1) / world / (alone.item() / 1e3) / 1e9,
-
                 "busbw_GBps": nbytes * 2 * (world - 1) / world / (t.item() / 1e3) / 1e9,
-                "nominal_GBps": 900.0, "bucket_dtype": args.bucket_dtype}
-        model.buckets.time_comm = False
+                "nominal_GBps": 900.0, "bucket_dtype": args.bucket_dtype,
+                "exposed_comm_ms": step_ms - ms_stub / args.steps,
+                "exposed_comm_frac": (step_ms - ms_stub / args.steps) / step_ms,
+                "step_ms_collective_stubbed": ms_stub / args.steps,
+                "ddp_overhead_ms": step_ms - ms_nosync / args.steps,
+                "step_ms_no_grad_sync": ms_nosync / args.steps,
+                "comm": bk.describe()}
 
     torch_gpu = None
     if rank == 0 and world == 1 and not args.no_torch_baseline:
@@ -390,33 +490,38 @@ def main():
         model = raw = opt = None
         torch.cuda.empty_cache()
         try:
-            torch_gpu = torch_gpu_baseline(dev)
+            torch_gpu = torch_gpu_baseline(dev, wl)
         except Exception as exc:  # informational only
             torch_gpu = {"error": repr(exc)[:200]}
     if rank == 0:
         cpu = None
         if not args.no_cpu_baseline:
-            tok_s, _, cores, sample = cpu_reference_run(2, 1)
+            tok_s, _, cores, sample = cpu_reference_run(wl, world, 4, 1)
             cpu = {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample}
         line = {
             "metric": "train_tokens_per_sec", "value": value, "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
+            "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "parallelism": f"dp{world}", "micro_steps_per_rank": accum,
-                       "l2": "inputs larger than L2: every micro-step streams ~6 GB of activations/weights (126 MB L2)",
+            "config": {"workload": wl["label"], "parallelism": f"dp{world}", "micro_steps_per_rank": accum,
+                       "tokens_per_step": tokens_per_step,
+                       "l2": ("inputs larger than L2: every micro-step streams several GB of activations/weights (126 MB L2)"
+                              if args.config != "char" else
+                              "inputs larger than L2: one micro-step streams ~1 GB of activations (126 MB L2)"),
                        "grad_allreduce": args.bucket_dtype if ddp else "none"},
             "mfu": {"flops_per_token": FLOPS_PER_TOKEN,
                     "vs_nominal_2.25PF": value * FLOPS_PER_TOKEN / (world * NOMINAL_BF16),
                     "vs_measured_peak": value * FLOPS_PER_TOKEN / (world * peaks["tf"] * 1e12),
-                    "measured_peak_tflops": peaks["tf"]},
+                    "vs_measured_sustained": value * FLOPS_PER_TOKEN / (world * peaks["tf_sus"] * 1e12),
+                    "measured_peak_tflops": peaks["tf"], "measured_sustained_tflops": peaks["tf_sus"]},
             "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "torch_gpu_baseline": torch_gpu,
+            "gpu_launches": int(launches), "loss_at_init": loss0, "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu,
         }
         if comm is not None:
             line["allreduce"] = comm
+            line["ddp_check"] = ddp_check
         emit(line)
     if ddp:
         dist.destroy_process_group()

@@ -65,7 +65,8 @@ int nsb_layernorm_bwd(const void* dy, int dy_dtype, const float* x, const float*
  * into the library (one copy per GPU that loads it, held until the process exits), so it serves
  * rows of at most 1024 columns (any number of rows) and fails with a message beyond that.  It
  * calls no cudaMalloc/cudaFree.  The first call on each device looks up the array's device address;
- * make that call before starting any stream capture.  All calls on a device share the one array
+ * make that call before starting any stream capture.  The address is that of the CURRENT device's
+ * copy: `stream` must belong to the current device (checked; the call fails otherwise).  All calls on a device share the one array
  * (nothing in it needs clearing between calls), therefore two calls that may run on the GPU at the
  * same time -- different streams, no ordering between them -- race on it: keep them ordered. */
 int nsb_layernorm_bwd_noalloc(const void* dy, int dy_dtype, const float* x, const float* w,

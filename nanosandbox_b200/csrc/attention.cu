@@ -631,11 +631,10 @@ int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const floa
     NSB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(dy) & 15) == 0,
                 "attention_bwd: qkv/dy must be 16-byte aligned");
     const int smem_dkv = 6 * fa::TILE_BYTES + 2 * 128 * 4, smem_dq = 6 * fa::TILE_BYTES;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDeviceOnce attr_done;
+    if (attr_done.first_use()) {
       cudaFuncSetAttribute(attn_bwd_dkv_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv);
       cudaFuncSetAttribute(attn_bwd_dq_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq);
-      attr_done = true;
     }
     dim3 grid((T + 63) / 64, B * H);
     const float sl2 = scale * 1.4426950408889634f;

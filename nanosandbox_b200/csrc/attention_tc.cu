@@ -645,19 +645,17 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
   int rc = make_tmap_2d(&tm, qkv, 2, static_cast<uint64_t>(3) * C, static_cast<uint64_t>(B) * T,
                         static_cast<uint64_t>(3) * C, HD, BQ);
   if (rc) return rc;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.first_use()) {
     cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     NSB_REQUIRE(e == cudaSuccess, "attention_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_done = true;
   }
   const dim3 grid(B * H, (T + BQ - 1) / BQ);
   if (g_attn_fwd_warps8 && g_attn_dbg == nullptr) {
-    static bool attr8 = false;
-    if (!attr8) {
+    static PerDeviceOnce attr8;
+    if (attr8.first_use()) {
       cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
       NSB_REQUIRE(e == cudaSuccess, "attention_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-      attr8 = true;
     }
     launch_pdl(attn_fwd_tc8_kernel, dim3(grid), dim3(320), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
                1.4426950408889634f / sqrtf(static_cast<float>(HD)));
@@ -1398,11 +1396,10 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
   if (rc) return rc;
   rc = make_tmap_2d(&tdq, dq_acc, 4, C, rows, C, 32, 128);
   if (rc) return rc;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.first_use()) {
     cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     NSB_REQUIRE(e == cudaSuccess, "attention_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_done = true;
   }
   const size_t items = rows * H * 8;
   launch_pdl(attn_delta_tc_kernel, dim3(static_cast<unsigned>((items + 255) / 256)), dim3(256), 0, stream, 
@@ -1410,11 +1407,10 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
   const dim3 grid(B * H, (T + BKV - 1) / BKV);
   const float scale = 1.0f / sqrtf(static_cast<float>(HD));
   if (g_attn_bwd_warps16 && g_attn_dbg == nullptr) {
-    static bool attr16 = false;
-    if (!attr16) {
+    static PerDeviceOnce attr16;
+    if (attr16.first_use()) {
       cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
       NSB_REQUIRE(e == cudaSuccess, "attention_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-      attr16 = true;
     }
     launch_pdl(attn_bwd_tc16_kernel, dim3(grid), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta,
                static_cast<__nv_bfloat16*>(dqkv), T, H, scale, scale * 1.4426950408889634f);

@@ -44,16 +44,34 @@ static inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   } while (0)
 
 static inline cudaStream_t cs(nsb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
-static inline int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
+static inline int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) dev = 0;
+  return dev & 63;
 }
+// SM count of the CURRENT device (cached per device: one process may drive several GPUs)
+static inline int sm_count() {
+  static int n[64] = {0};
+  const int dev = current_device();
+  if (n[dev] == 0) {
+    int v = 0;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    n[dev] = v > 0 ? v : 148;
+  }
+  return n[dev];
+}
+// Function attributes (opt-in shared memory) are per device: a launcher keeps one of these as a
+// function-local static and sets its attributes when first_use() says this device has not been seen.
+// Racing threads at worst set the same attribute twice.
+struct PerDeviceOnce {
+  unsigned long long seen = 0;
+  bool first_use() {
+    const unsigned long long bit = 1ull << current_device();
+    if (seen & bit) return false;
+    seen |= bit;
+    return true;
+  }
+};
 
 // ---- device helpers ------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -302,8 +302,10 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
   } else {
     const float invC = 1.0f / static_cast<float>(C);
     // two groups of kLnRows warps take alternate slabs (four consumer warps per SM sub-partition hide the
-    // shared-memory and shuffle latencies of one another); every warp observes every slab's barrier so that
-    // the phases are seen in order, and processes / releases only its own group's slabs
+    // shared-memory and shuffle latencies of one another).  The ring depth is a multiple of kLnGroups (the
+    // launcher guarantees it), so a ring slot always belongs to the same group: a warp waits only on the
+    // slots its own group releases, the producer cannot refill such a slot before this warp has arrived
+    // on its `empty` barrier, and the parity wait below can therefore never alias a later phase.
     const int cg = warp / kLnRows, wr = warp % kLnRows;   // consumer group, row within the slab
     int it = 0;
     int g = blockIdx.x;
@@ -313,9 +315,9 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
       if (g0 < ngroups && g0 * kLnRows + wr < M) { mu_n = mean[g0 * kLnRows + wr]; rs_n = rstd[g0 * kLnRows + wr]; }
     }
     for (; g < ngroups; g += gridDim.x, ++it) {
+      if ((it % kLnGroups) != cg) continue;
       const int s = it % nstages;
       ptx::mbar_wait(&full[s], (it / nstages) & 1);
-      if ((it % kLnGroups) != cg) continue;
       const int row = g * kLnRows + wr;
       const float mu = mu_n, rs = rs_n;
       const int gn = g + kLnGroups * gridDim.x;           // statistics of this group's next slab, one turn ahead
@@ -1090,6 +1092,7 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
   const size_t slab = kLnRows * (dy_row + static_cast<size_t>(C) * 4 * (dres_in != nullptr ? 2 : 1));
   int nstages = static_cast<int>((200 * 1024) / slab);
   if (nstages > 4) nstages = 4;
+  nstages -= nstages % kLnGroups;   // a ring slot must always fall to the same consumer group (see the kernel)
   const bool stream_ok = (dy_row % 16 == 0) && (C % 4 == 0) && nstages >= 2 && M >= 4 * kLnRows &&
                          static_cast<size_t>(nstages) * slab >= static_cast<size_t>(kLnWarps) * 128 * nv * 4;
   if (stream_ok) {
@@ -1195,11 +1198,10 @@ int nsb_cross_entropy_fwd_bwd(void* logits, int dtype, const int64_t* targets, f
   const size_t smem = static_cast<size_t>(ld) * 2;
   NSB_REQUIRE(smem <= 232448 - 1024, "cross_entropy_fwd_bwd: a row of %d logits does not fit in shared memory; "
               "use the separate passes", ld);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_set;
+  if (attr_set.first_use()) {
     cudaError_t e = cudaFuncSetAttribute(cross_entropy_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024);
     NSB_REQUIRE(e == cudaSuccess, "cross_entropy_fwd_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_set = true;
   }
   launch_pdl(cross_entropy_fused_kernel, dim3(M), dim3(kCeFusedThreads), smem, cs(stream),
              static_cast<__nv_bfloat16*>(logits), targets, lse, row_loss, V, ld);
@@ -1352,6 +1354,17 @@ extern "C" int nsb_layernorm_bwd_noalloc(const void* dy, int dy_dtype, const flo
               "use nsb_layernorm_bwd with caller-provided scratch",
               C, kNoAllocMaxC);
   NSB_REQUIRE(M >= 0, "layernorm_bwd_noalloc: negative row count %d", M);
+  // The built-in array is looked up for the CURRENT device; a stream that belongs to another device
+  // would run the kernels there with this device's address.  Refuse instead of corrupting memory.
+  if (stream != nullptr) {
+    int cur = -1, sdev = -1;
+    if (cudaGetDevice(&cur) == cudaSuccess && cudaStreamGetDevice(cs(stream), &sdev) == cudaSuccess)
+      NSB_REQUIRE(cur == sdev,
+                  "layernorm_bwd_noalloc: the stream belongs to device %d but device %d is current; "
+                  "make the stream's device current before the call", sdev, cur);
+    else
+      (void)cudaGetLastError();   // could not tell (e.g. a capturing stream): proceed with the current device
+  }
   float* scratch = nullptr;
   const int rc = builtin_scratch_for_current_device(&scratch);
   if (rc != 0) return rc;

@@ -890,11 +890,10 @@ struct LaunchPlan {
 template <int BN, bool A_MN, bool B_MN, int CG, int NGRP = 2>
 static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_t stream) {
   auto kern = gemm_tc_kernel<BN, A_MN, B_MN, CG, NGRP>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.first_use()) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemLimit));
     NSB_REQUIRE(e == cudaSuccess, "gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_done = true;
   }
   const size_t smem = smem_bytes_for(BN / CG, lp.stages, lp.nbuf * lp.ngroups);
   const int total = lp.num_m * lp.num_n * lp.splits;

@@ -49,11 +49,20 @@ def write_dataset(data_dir: str, vocab_size: int, kind: str = "uniform", n: int 
         tr, va = markov_stream(vocab_size, n, seed), markov_stream(vocab_size, max(n // 8, 4096), seed + 1)
     else:
         raise ValueError(f"unknown synthetic kind {kind!r}")
-    tr.tofile(os.path.join(data_dir, "train.bin"))
-    va.tofile(os.path.join(data_dir, "val.bin"))
+    # write under temporary names and rename into place (val.bin, then meta.pkl, train.bin last: readers
+    # test for train.bin), so that a concurrent reader never maps a partly written file
+    tag = f".tmp{os.getpid()}"
+    final = []
+    va.tofile(os.path.join(data_dir, "val.bin" + tag))
+    final.append("val.bin")
     if vocab_size < 50000:  # char-level datasets carry their vocab in meta.pkl; GPT-2 BPE ones do not
-        with open(os.path.join(data_dir, "meta.pkl"), "wb") as f:
+        with open(os.path.join(data_dir, "meta.pkl" + tag), "wb") as f:
             pickle.dump({"vocab_size": vocab_size}, f)
+        final.append("meta.pkl")
+    tr.tofile(os.path.join(data_dir, "train.bin" + tag))
+    final.append("train.bin")
+    for name in final:
+        os.replace(os.path.join(data_dir, name + tag), os.path.join(data_dir, name))
 
 
 def get_batch(data: np.ndarray, batch_size: int, block_size: int, device, pin: bool = True):

@@ -17,6 +17,7 @@ DDP numerics (scale in place, all-reduce the fp32 slice itself).
 from __future__ import annotations
 
 import contextlib
+import os
 from typing import Callable, List, Optional, Tuple
 
 import torch
@@ -44,6 +45,15 @@ class GradBucketManager:
         self.bytes_reduced = 0
         self.comm_events: List[Tuple[object, object]] = []
         self.time_comm = False
+        self.stub_collective = False    # measurement hook: skip the collective itself (pack / unpack still run)
+        self.comm_info = {}
+
+    def all_reduce(self, t: torch.Tensor) -> None:
+        if not self.stub_collective:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.pg)
+
+    def describe(self) -> dict:
+        return dict(self.comm_info, buckets=len(self.ranges), bucket_dtype=self.bucket_dtype)
 
     def reduce_bucket(self, k: int) -> None:
         s, e = self.ranges[k]
@@ -64,12 +74,12 @@ class GradBucketManager:
             if self.bucket_dtype == "bf16":
                 st = self.staging[s:e]
                 self.pack(g, st, inv)                       # cast fp32 -> bf16 and scale by 1/world
-                dist.all_reduce(st, op=dist.ReduceOp.SUM, group=self.pg)
+                self.all_reduce(st)
                 self.unpack(st, g)                          # bf16 -> fp32 back into the arena slice
                 self.bytes_reduced += st.numel() * 2
             else:
                 self.scale(g, inv)                          # divide first, then sum: DDP's order
-                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.pg)
+                self.all_reduce(g)
                 self.bytes_reduced += g.numel() * 4
             if t0 is not None:
                 t1.record()
@@ -85,24 +95,55 @@ class GradBucketManager:
         self.launched = []
 
 
+def gradient_communicator(max_ctas: int):
+    """A communicator of its own for the gradient all-reduce, with a bound on the CTAs NCCL may put on the
+    GPU (ncclConfig_t.maxCTAs).  The buckets are reduced while the last micro-step's backward is still
+    running; every SM an NCCL CTA occupies is an SM a GEMM CTA cannot use, and over NVLink 5 / NVSwitch a
+    few CTAs already move 250 MB in about a millisecond, far inside the ~14 ms of backward it hides under.
+    Returns (process_group, info)."""
+    info = {"communicator": "default process group", "max_ctas": None}
+    if max_ctas <= 0 or dist.get_backend() != "nccl":
+        return None, info
+    try:
+        from torch.distributed import ProcessGroupNCCL
+        opts = ProcessGroupNCCL.Options()
+        opts.is_high_priority_stream = True
+        opts.config.max_ctas = int(max_ctas)
+        opts.config.min_ctas = 1
+        pg = dist.new_group(ranks=list(range(dist.get_world_size())), backend="nccl", pg_options=opts)
+        info = {"communicator": "dedicated NCCL communicator (high-priority stream)", "max_ctas": int(max_ctas)}
+        return pg, info
+    except Exception as exc:  # an NCCL / torch build without the config field: keep the default group
+        info["note"] = f"dedicated communicator unavailable: {type(exc).__name__}: {exc}"[:200]
+        return None, info
+
+
 class DistributedDataParallel:
     def __init__(self, module, device_ids=None, process_group=None, bucket_dtype: str = "bf16",
-                 broadcast_parameters: bool = True):
+                 broadcast_parameters: bool = True, max_ctas: Optional[int] = None):
         from . import ops
         self.module = module
         self.require_backward_grad_sync = True
-        self.process_group = process_group
         self.world_size = dist.get_world_size(process_group)
+        comm_info = {"communicator": "caller's process group", "max_ctas": None}
+        if process_group is None:
+            if max_ctas is None:
+                max_ctas = int(os.environ.get("NSB_NCCL_MAX_CTAS", "8"))
+            grad_pg, comm_info = gradient_communicator(max_ctas)
+        else:
+            grad_pg = process_group
+        self.process_group = process_group
         arena = module.arena()
         if broadcast_parameters:
             # one broadcast over the flat parameter arena (DDP: _sync_module_states, 250 MiB chunks)
             dist.broadcast(arena.params, src=0, group=process_group)
             arena.lowp_version = -1
         self.buckets = GradBucketManager(
-            arena.grads, module.bucket_ranges, self.world_size, process_group, bucket_dtype,
+            arena.grads, module.bucket_ranges, self.world_size, grad_pg, bucket_dtype,
             pack=lambda g, st, inv: ops.cast_f32_to_bf16(g, st, inv),
             unpack=lambda st, g: ops.cast_bf16_to_f32(st, g),
             scale=lambda g, inv: ops.scale_f32(g, inv))
+        self.buckets.comm_info = comm_info
         module._grad_sync = self
 
     # hooks called by GPT._engine_backward on the compute stream

@@ -29,6 +29,9 @@ from ._lib import EPI_ACCUM, EPI_DGELU, EPI_GELU, EPI_RESIDUAL, EPI_STORE, NsbEr
 from .arena import ParamArena, bucket_ranges, ready_order
 
 
+MAX_N_EMBD = 1024   # widest row the LayerNorm kernels take (csrc/elementwise.cu: nsb_layernorm_fwd / _bwd)
+
+
 @dataclass
 class GPTConfig:
     block_size: int = 1024
@@ -93,13 +96,15 @@ class _Acts:
     """Activation + scratch buffers for one (B, T, precision) shape; allocated once and reused
     every micro-step (torch owns the memory, nothing is allocated inside the step)."""
 
-    def __init__(self, cfg: GPTConfig, B: int, T: int, lowp: bool, device):
+    def __init__(self, cfg: GPTConfig, B: int, T: int, lowp: bool, device, train: bool = True):
         C, L, H = cfg.n_embd, cfg.n_layer, cfg.n_head
         M = B * T
         adt = torch.bfloat16 if lowp else torch.float32
         f32 = torch.float32
         new = lambda *shape, dtype=adt: torch.empty(*shape, dtype=dtype, device=device)
         self.B, self.T, self.M, self.lowp, self.adt = B, T, M, lowp, adt
+        self.train = train
+        self.gen = 0            # bumped by every forward that overwrites these buffers
         self.x = [new(M, C, dtype=f32) for _ in range(L + 1)]       # residual stream, block inputs
         self.xmid = [new(M, C, dtype=f32) for _ in range(L)]         # after attention
         self.ln1 = [new(M, C) for _ in range(L)]
@@ -113,10 +118,16 @@ class _Acts:
         self.lnf = new(M, C)
         self.statf = [new(M, dtype=f32) for _ in range(2)]
         self.ldv = (cfg.vocab_size + 7) // 8 * 8                     # 16-byte rows for TMA / 128-bit IO
+        self.logits_last = new(B, self.ldv)
+        self.idx = None
+        self.targets = None
+        self.stats = None
+        if not train:
+            # forward(idx, targets=None): last-position logits only; no [M, V] logits, no backward scratch
+            return
         self.logits = new(M, self.ldv)
         if self.ldv != cfg.vocab_size:
             self.logits.zero_()
-        self.logits_last = new(B, self.ldv)
         self.ce_lse = new(M, dtype=f32)
         self.ce_row = new(M, dtype=f32)
         # backward scratch
@@ -130,9 +141,6 @@ class _Acts:
         # fp32 dQ accumulator of the tensor-core attention backward (kept all-zero between calls)
         self.dq_acc = torch.zeros(M, C, dtype=f32, device=device) if (lowp and C // H == 64) else None
         self.ln_scratch = torch.empty(ops.layernorm_bwd_scratch_bytes(M, C) // 4, dtype=f32, device=device)
-        self.idx = None
-        self.targets = None
-        self.stats = None
 
 
 class _FusedStep(torch.autograd.Function):
@@ -144,15 +152,23 @@ class _FusedStep(torch.autograd.Function):
     def forward(ctx, anchor, model, idx, targets):
         logits, loss = model._engine_forward(idx, targets, for_backward=True)
         ctx.model = model
-        ctx.mark_non_differentiable(logits)
-        ctx.set_materialize_grads(False)  # no [B,T,V] zeros tensor for the unused logits gradient
-        return logits, loss
+        ctx.acts = model._last_acts
+        ctx.gen = ctx.acts.gen
+        model._step_logits = logits        # handed to GPT.forward outside the autograd node
+        ctx.set_materialize_grads(False)
+        return loss
 
     @staticmethod
-    def backward(ctx, _glogits, gloss):
+    def backward(ctx, gloss):
         if gloss is None:
             return None, None, None, None
-        ctx.model._engine_backward(gloss)
+        a = ctx.acts
+        if a.gen != ctx.gen:
+            raise NsbError(
+                "backward() of a forward whose activations have been overwritten: another forward with the "
+                "same (batch, block, precision) ran in between (the engine keeps one set of activation "
+                "buffers per shape). Call loss.backward() before the next forward of that shape.")
+        ctx.model._engine_backward(gloss, a)
         return None, None, None, None
 
 
@@ -161,6 +177,8 @@ class GPT(nn.Module):
         super().__init__()
         assert config.vocab_size is not None
         assert config.block_size is not None
+        if config.n_embd > MAX_N_EMBD or config.n_embd % 4 != 0:
+            raise NsbError(f"n_embd={config.n_embd}: the LayerNorm kernels need a multiple of 4 up to {MAX_N_EMBD}")
         self.config = config
         # same constructors in the same order as nanoGPT -> same consumption of the global RNG,
         # so get_batch() draws the same indices afterwards (hard parts)
@@ -181,13 +199,15 @@ class GPT(nn.Module):
             print("number of parameters: %.2fM" % (self.get_num_params() / 1e6,))
         self._arena: ParamArena | None = None
         self._acts = {}
+        self._infer_acts = None
+        self._step_logits = None
         self._grad_sync = None          # set by nanosandbox_b200.ddp.DistributedDataParallel
         # bf16 path: GELU as its own memory-bound kernels (faster on B200 than the fused GEMM epilogues,
         # whose eight epilogue warps cannot hide the erf math behind a K = 768 mainloop)
         self.split_gelu = os.environ.get("NSB_SPLIT_GELU", "1") != "0"
         # Training forward (bf16): the loss kernel also leaves softmax - onehot in the logits buffer (one
-        # pass over the 1.2 GB of logits instead of two), so the `logits` returned next to the loss then
-        # hold that gradient, not the logits.  Set to False if you read the logits of a training forward.
+        # pass over the 1.2 GB of logits instead of two).  The logits no longer exist after that, so such
+        # a forward returns (None, loss).  Set to False if you read the logits of a training forward.
         self.fuse_loss_backward = True
         # Weight-gradient GEMMs run on a side stream: nothing in the backward chain depends on them, so
         # their CTAs fill the SMs that the chain's kernels leave idle in their ramp-up and tail.
@@ -216,6 +236,7 @@ class GPT(nn.Module):
         self.config.block_size = block_size
         self._arena = None
         self._acts = {}
+        self._infer_acts = None
         self.transformer.wpe.weight = nn.Parameter(self.transformer.wpe.weight.detach()[:block_size].clone())
 
     @classmethod
@@ -240,6 +261,9 @@ class GPT(nn.Module):
         """nanoGPT's from_pretrained: loads OpenAI GPT-2 weights through the Hugging Face hub (needs the
         weights in the local HF cache or network access)."""
         assert model_type in {"gpt2", "gpt2-medium", "gpt2-large", "gpt2-xl"}
+        if model_type in ("gpt2-large", "gpt2-xl"):
+            raise NsbError(f"from_pretrained({model_type!r}): n_embd > {MAX_N_EMBD} is not supported by the "
+                           "LayerNorm kernels of this library (gpt2 and gpt2-medium are)")
         override_args = override_args or {}
         assert all(k == "dropout" for k in override_args)
         from transformers import GPT2LMHeadModel
@@ -317,6 +341,7 @@ class GPT(nn.Module):
         self._names = {id(p): n for n, p in named}
         self._arena = arena
         self._acts = {}
+        self._infer_acts = None
         self._has_bias = self.config.bias
         self.bucket_ranges = bucket_ranges(arena, self.config.n_layer, self.config.bias)
         return arena
@@ -327,6 +352,7 @@ class GPT(nn.Module):
         if ar is not None and self.lm_head.weight.data_ptr() != ar.p("transformer.wte.weight").data_ptr():
             self._arena = None  # storage moved (e.g. .to(other device)): rebuild lazily
             self._acts = {}
+            self._infer_acts = None
         return out
 
     def load_state_dict(self, state_dict, *a, **k):
@@ -356,7 +382,9 @@ class GPT(nn.Module):
             raise NotImplementedError("dropout > 0 is not implemented in the fused path yet "
                                       "(pass --dropout=0.0, as the reference's own runs do)")
         if targets is not None and torch.is_grad_enabled() and self.lm_head.weight.requires_grad:
-            return _FusedStep.apply(self.lm_head.weight, self, idx, targets)
+            loss = _FusedStep.apply(self.lm_head.weight, self, idx, targets)
+            logits, self._step_logits = self._step_logits, None
+            return logits, loss
         return self._engine_forward(idx, targets)
 
     def _mode_lowp(self) -> bool:
@@ -369,12 +397,26 @@ class GPT(nn.Module):
             raise NotImplementedError(f"autocast dtype {dt} is not supported (bfloat16 or float32)")
         return False
 
-    def _get_acts(self, B, T, lowp) -> _Acts:
+    _MAX_TRAIN_SHAPES = 4
+
+    def _get_acts(self, B, T, lowp, train=True) -> _Acts:
+        """Activation buffers for this shape.  Training/eval shapes (targets given) are cached, a few
+        at a time (train batch + eval batch); the inference path (targets=None, e.g. generate(),
+        which calls forward with a new T for every token) keeps ONE forward-only set and replaces it
+        when the shape changes, so its memory does not grow with the number of generated tokens."""
+        if not train:
+            a = self._infer_acts
+            if a is None or (a.B, a.T, a.lowp) != (B, T, lowp):
+                self._infer_acts = None      # release before allocating the replacement
+                a = self._infer_acts = _Acts(self.config, B, T, lowp, self.lm_head.weight.device, train=False)
+            return a
         key = (B, T, lowp)
-        a = self._acts.get(key)
+        a = self._acts.pop(key, None)
         if a is None:
+            while len(self._acts) >= self._MAX_TRAIN_SHAPES:
+                self._acts.pop(next(iter(self._acts)))      # least recently used
             a = _Acts(self.config, B, T, lowp, self.lm_head.weight.device)
-            self._acts[key] = a
+        self._acts[key] = a                                 # most recently used last
         return a
 
     def _engine_forward(self, idx, targets, for_backward=False):
@@ -387,7 +429,8 @@ class GPT(nn.Module):
         C, L, H, V = cfg.n_embd, cfg.n_layer, cfg.n_head, cfg.vocab_size
         D = C // H
         M = B * T
-        a = self._get_acts(B, T, lowp)
+        a = self._get_acts(B, T, lowp, train=targets is not None)
+        a.gen += 1               # a backward() of an earlier forward on these buffers is now invalid
         st = ops.stream_handle()
         if lowp:
             self._refresh_lowp(arena, st)
@@ -435,15 +478,18 @@ class GPT(nn.Module):
         else:
             ops.cross_entropy_fwd(a.logits, targets, a.ce_lse, a.ce_row, a.stats, V, st)
         self._last_acts = a
+        if a.ce_fused:
+            # the buffer now holds softmax - onehot, not logits: hand back None rather than a tensor
+            # that is not what its name says (set GPT.fuse_loss_backward = False to get the logits)
+            return None, a.stats[0]
         # NOTE: the logits buffer is reused: backward() turns it into dlogits in place and the next
         # forward overwrites it.  Clone it if you need the values later.
         return a.logits[:, :V].view(B, T, V), a.stats[0]
 
     # ------------------------------------------------------------------ backward
-    def _engine_backward(self, gloss):
+    def _engine_backward(self, gloss, a: _Acts):
         cfg = self.config
         arena = self._arena
-        a: _Acts = self._last_acts
         lowp = a.lowp
         B, T, M = a.B, a.T, a.M
         C, L, H, V = cfg.n_embd, cfg.n_layer, cfg.n_head, cfg.vocab_size

@@ -33,17 +33,11 @@ p0 = m.arena().params.clone(); dist.broadcast(p0, 0)
 assert torch.equal(p0, m.arena().params), "rank-0 broadcast failed"
 g = torch.Generator().manual_seed(100 + rank)
 accum = 3
-local = torch.zeros_like(m.arena().grads)
 for micro in range(accum):
     x = torch.randint(0, 1000, (4, 128), generator=g).to(dev); y = torch.randint(0, 1000, (4, 128), generator=g).to(dev)
     d.require_backward_grad_sync = micro == accum - 1
-    if micro == accum - 1:
-        local.copy_(m.arena().grads)       # accumulated so far, before the synchronising backward
     _, loss = d(x, y)
     (loss / accum).backward()
-    if micro == accum - 1:
-        # recompute this micro-step's own contribution without sync to finish `local`
-        pass
 torch.cuda.synchronize()
 synced = m.arena().grads.clone()
 # reference: redo the same three micro-steps without any sync, then mean-allreduce

@@ -349,6 +349,37 @@ def test_gemm_wgrad_accum(dt, accumulate, M, N, K):
     _gemm_case(dt, M, N, K, False, False, _lib.EPI_ACCUM, accumulate=accumulate, alpha=0.125)
 
 
+# The three lm_head GEMMs of the headline configuration (cfg4: M = 12 x 1024 tokens, C = 768, V = 50304): 31 % of the
+# step's GEMM FLOPs.  The two gradient GEMMs read the 1.2 GB dlogits, which is what switches the tile walk
+# to n-fastest and picks the split-K plan at M = 50304; no smaller shape reaches those branches by policy.
+@pytest.mark.parametrize("which", ["fwd", "dgrad", "wgrad"])
+def test_gemm_lm_head_headline_shapes(which):
+    T, Cc, V = 12288, 768, 50304
+    if which == "fwd":       # logits[T, V] = lnf[T, C] . wte[V, C]^T
+        _gemm_case(torch.bfloat16, T, V, Cc, True, True, _lib.EPI_STORE)
+    elif which == "dgrad":   # dlnf[T, C] = alpha * dlogits[T, V] . wte[V, C]   (B read MN-major in place)
+        _gemm_case(torch.bfloat16, T, Cc, V, True, False, _lib.EPI_STORE, alpha=1.0 / T)
+    else:                    # dwte[V, C] += alpha * dlogits^T[V, T] . lnf[T, C] (both MN-major, split-K, n-fastest walk)
+        _gemm_case(torch.bfloat16, V, Cc, T, False, False, _lib.EPI_ACCUM, accumulate=True, alpha=1.0 / T)
+
+
+@pytest.mark.parametrize("walk", [8, 9])
+@pytest.mark.parametrize("epi,a_k,b_k,M,N,K", [
+    (_lib.EPI_STORE, True, True, 2048, 1280, 256),
+    (_lib.EPI_STORE, True, False, 1536, 768, 1024),
+    (_lib.EPI_ACCUM, False, False, 2304, 768, 2048),
+    (_lib.EPI_RESIDUAL, True, True, 4000, 1160, 192),
+])
+def test_gemm_tc_tile_walk_orders(walk, epi, a_k, b_k, M, N, K):
+    """m-fastest (8) and n-fastest (9) tile walks forced on shapes with several tiles per CTA."""
+    lib = _lib.load()
+    lib.nsb_gemm_debug_config(0, 0, walk)
+    try:
+        _gemm_case(torch.bfloat16, M, N, K, a_k, b_k, epi, accumulate=True, alpha=0.5)
+    finally:
+        lib.nsb_gemm_debug_config(0, 0, 0)
+
+
 def test_gemm_tc_matches_simt_path():
     """The tcgen05 kernel against our own exact SIMT kernel on identical bf16 inputs."""
     torch.manual_seed(7)

@@ -119,16 +119,27 @@ ctx = nullcontext() if dtype == 'float32' else torch.amp.autocast(device_type='c
 # -----------------------------------------------------------------------------
 # data: train.bin / val.bin of uint16 tokens (+ meta.pkl), as nanoGPT's prepare.py leaves them
 data_dir = os.path.join('data', dataset)
-if not os.path.exists(os.path.join(data_dir, 'train.bin')):
+# Whether the data has to be synthesised is decided collectively (any rank without train.bin -> yes), so all
+# ranks take the same collectives in the same order.  One writer per node (LOCAL_RANK 0: in the 8-Pod
+# StatefulSet every Pod has its own filesystem) writes the seeded stream (identical everywhere) to temporary
+# names and renames them into place, meta.pkl last, so no reader ever sees a partly written file.
+need_synth = not os.path.exists(os.path.join(data_dir, 'train.bin'))
+if ddp:
+    flag = torch.tensor([int(need_synth)], device=device)
+    torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MAX)
+    need_synth = bool(flag.item())
+if need_synth:
     if not synthetic:
         raise SystemExit(f"{data_dir}/train.bin not found and --synthetic=False")
     from nanosandbox_b200.data import write_dataset
     vocab = synthetic_vocab or (65 if dataset.endswith('_char') else 50304)
-    if master_process:
-        print(f"{data_dir}/train.bin not found: writing a seeded synthetic {synthetic_kind} stream, vocab {vocab}")
-        write_dataset(data_dir, vocab, kind=synthetic_kind)
-    if ddp:
-        torch.distributed.barrier()
+    if (not ddp) or ddp_local_rank == 0:
+        if master_process:
+            print(f"{data_dir}/train.bin not found: writing a seeded synthetic {synthetic_kind} stream, vocab {vocab}")
+        if not os.path.exists(os.path.join(data_dir, 'train.bin')):
+            write_dataset(data_dir, vocab, kind=synthetic_kind)
+if ddp:
+    torch.distributed.barrier()
 
 
 def get_batch(split):
