@@ -338,8 +338,9 @@ def main():
     # ---- warm-up (the first step doubles as the sanity check: a random-init model must sit at ln V), then the
     #      device-resident timed region ("value") ----
     loss0 = train_step(resident, False).item() * accum
-    if not abs(loss0 - math.log(V)) < 0.2:
-        raise SystemExit(f"bench.py: loss at init {loss0:.4f} is not within 0.2 of ln({V}) = {math.log(V):.4f}: "
+    loss_tol = 0.35 if CFG["n_embd"] > 768 else 0.2      # wider models start with more logit variance
+    if not abs(loss0 - math.log(V)) < loss_tol:
+        raise SystemExit(f"bench.py: loss at init {loss0:.4f} is not within {loss_tol} of ln({V}) = {math.log(V):.4f}: "
                          "the step is not computing the model")
     for _ in range(args.warmup - 1):
         train_step(resident, False)

@@ -66,6 +66,7 @@ DEBUG_SIGNATURES = {
     "nsb_gemm_debug_timing": (None, [_P]),
     "nsb_gemm_debug_pdl": (None, [_I]),
     "nsb_gemm_debug_pipeline": (None, [_I, _I, _I]),
+    "nsb_gemm_debug_scheduler": (None, [_I]),
     "nsb_attention_debug_config": (None, [_I]),
     "nsb_attention_debug_timing": (None, [_P]),
 }
@@ -92,6 +93,8 @@ def load() -> C.CDLL:
         lib.nsb_attention_debug_config(int(os.environ["NSB_ATTN_MODE"]))
     if os.environ.get("NSB_GEMM_PDL", "1") == "0":  # A/B switch for the dependent-launch overlap
         lib.nsb_gemm_debug_pdl(0)
+    if os.environ.get("NSB_GEMM_DYNAMIC", "1") == "0":  # A/B switch: fixed-stride tile walk instead of the tile counter
+        lib.nsb_gemm_debug_scheduler(0)
     _lib = lib
     return lib
 

@@ -14,6 +14,7 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
 // warps 2..5 (and 6..9 for the ALU-heavy GELU epilogues) = epilogue, one TMEM lane quarter each.
+#include <atomic>
 #include <mutex>
 #include <unordered_map>
 
@@ -170,6 +171,18 @@ __device__ __forceinline__ void epilogue_row32(const EpiParams& p, int m, int n,
   }
 }
 
+// ---- dynamic tile scheduler ---------------------------------------------------------------------
+// The persistent CTAs (or CTA pairs) of a launch draw tile numbers from a counter in global memory
+// instead of walking a fixed stride.  A CTA that cannot get an SM for a while (another kernel, e.g. an
+// NCCL all-reduce running beside backward, holds it: a GEMM CTA needs the whole register file) then
+// simply takes no tiles and the CTAs that are running absorb its share, where a static walk leaves
+// its share to a second wave.  Each launch uses the next of kSchedSlots counters (launches of
+// different streams may overlap); the last unit to finish puts its counter pair back to zero.
+constexpr int kSchedSlots = 1024;
+constexpr int kTileQ = 4;                 // depth of the per-CTA queue of tile numbers
+__device__ int g_tile_next[kSchedSlots];
+__device__ int g_tile_done[kSchedSlots];
+
 // ---- the kernel -------------------------------------------------------------------------------
 struct TileCoord { int m_blk, n_blk, split; };
 // m-fastest walk: concurrently running tiles share the B panel, A panels stream (good when A fits
@@ -206,7 +219,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
                    const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
                    const __grid_constant__ CUtensorMap tma_aux, int K, int num_m, int num_n, int splits,
                    int kb_per_split, int stages, int nbuf, int tma_epi, int ngroups, int aux_direct, int n_fast,
-                   int pipe_epi, EpiParams ep, long long* dbg) {
+                   int pipe_epi, int sched_slot, EpiParams ep, long long* dbg) {
   // per-CTA wall-clock trace (debug buffer of >= 8192 words): ns since boot at 8 points of the CTA's life
   auto gstamp_if = [&](bool who, int slot) {
     if (dbg != nullptr && who) {
@@ -238,7 +251,11 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
   uint64_t* auxfull = tempty + 2;                    // [group][buffer]: aux tile landed (and buffer free)
   uint64_t* staged = auxfull + kMaxBuf;              // [group][buffer]: output data staged by the 128 threads
   uint64_t* freeb = staged + kMaxBuf;                // [group][buffer]: TMA store drained the buffer
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(freeb + kMaxBuf);
+  uint64_t* qfull = freeb + kMaxBuf;                 // tile queue: entry written (by the leader's producer)
+  uint64_t* qempty = qfull + kTileQ;                 // ... entry read by every consumer warp of the CTA / pair
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(qempty + kTileQ);
+  volatile int* tile_q = reinterpret_cast<volatile int*>(tmem_slot + 1);
+  const bool dyn = sched_slot >= 0;
 
   // Hardware warps: 0 .. 4*NGRP-1 epilogue (TMEM -> registers -> staging smem), 4*NGRP .. 5*NGRP-1 one
   // store warp per epilogue group (issues the TMA stores / aux loads, recycles staging buffers), then
@@ -248,6 +265,10 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
   const int warp = hw_warp >= 5 * NGRP ? hw_warp - 5 * NGRP : (hw_warp >= 4 * NGRP ? -1 : hw_warp + 2);
   const int total_kb = (K + BK - 1) / BK;
   const int total_work = num_m * num_n * splits;
+  // first tile number of this unit, requested before the set-up below so that its latency hides there (the
+  // counter belongs to this launch alone; nothing of the previous kernel is read)
+  int w_next = -1;
+  if (sched_slot >= 0 && rank == 0 && warp == 0 && lane == 0) w_next = atomicAdd(&g_tile_next[sched_slot], 1);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tma_a);
@@ -261,11 +282,15 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
   if (warp == 0) {
     // the 44 barriers are initialised by the lanes of one warp side by side (a single thread doing it
     // in turn was most of the CTA's set-up time)
-    constexpr int kBars = 2 * kMaxStages + 4 + 3 * kMaxBuf;
+    constexpr int kBars = 2 * kMaxStages + 4 + 3 * kMaxBuf + 2 * kTileQ;
+    // warps that read the tile queue, per CTA: the MMA issuer (leader) or the producer (peer CTA of a pair),
+    // the active epilogue warps, and the store warps of the staged epilogue
+    const uint32_t qreaders = static_cast<uint32_t>(CG * (1 + 4 * ngroups + (tma_epi ? ngroups : 0)));
     for (int i = lane; i < kBars; i += 32) {
-      uint32_t count = 1;                                                   // full, empty, tfull, auxfull, freeb
+      uint32_t count = 1;                                                   // full, empty, tfull, auxfull, freeb, qfull
       if (i >= 2 * kMaxStages + 2 && i < 2 * kMaxStages + 4) count = 4 * ngroups * CG;   // tempty: epilogue warps of both CTAs
       else if (i >= 2 * kMaxStages + 4 + kMaxBuf && i < 2 * kMaxStages + 4 + 2 * kMaxBuf) count = 128;  // staged
+      else if (i >= 2 * kMaxStages + 4 + 3 * kMaxBuf + kTileQ) count = qreaders;         // qempty (on the leader)
       ptx::mbar_init(&bars[i], count);
     }
     ptx::fence_mbar_init();
@@ -286,6 +311,26 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
   pdl_trigger();
   gstamp(2);
 
+  // Tile sequence of this CTA.  Static: unit, unit + nunits, ...  Dynamic: the leader's producer draws the
+  // numbers from the global counter and queues them (in both CTAs of a pair); every other role reads the
+  // queue in order.  -1 ends the sequence.  All lanes of a warp call next_tile() together.
+  int q_seq = 0;
+  auto next_tile = [&]() -> int {
+    if (!dyn) {
+      const int w = unit + q_seq * nunits;
+      ++q_seq;
+      return w < total_work ? w : -1;
+    }
+    const int slot = q_seq & (kTileQ - 1);
+    const uint32_t ph = static_cast<uint32_t>(q_seq / kTileQ) & 1u;
+    if (CG == 2) ptx::mbar_wait_cluster(&qfull[slot], ph); else ptx::mbar_wait(&qfull[slot], ph);
+    const int w = tile_q[slot];
+    __syncwarp();
+    if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&qempty[slot], 0); else ptx::mbar_arrive(&qempty[slot]); }
+    ++q_seq;
+    return w;
+  };
+
   if (warp == 0) {
     // ================================ TMA producer ==========================================
     // lane 0 owns the barrier protocol; the boxes of a stage (up to 6 for MN-major operands) are
@@ -295,7 +340,31 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       uint32_t phase = 0;
       constexpr int A_BOXES = A_MN ? BM / 64 : 1;
       constexpr int B_BOXES = B_MN ? BNL / 64 : 1;
-      for (int w = unit; w < total_work; w += nunits) {
+      const bool fetcher = dyn && rank == 0;    // draws from the global counter and feeds the queue(s)
+      int pub = 0;
+      while (true) {
+        int w;
+        if (fetcher) {
+          if (lane == 0) {
+            if (w_next >= total_work) w_next = -1;
+            const int slot = pub & (kTileQ - 1);
+            const uint32_t qph = (static_cast<uint32_t>(pub / kTileQ) & 1u) ^ 1u;
+            if (CG == 2) ptx::mbar_wait_cluster(&qempty[slot], qph); else ptx::mbar_wait(&qempty[slot], qph);
+            tile_q[slot] = w_next;
+            if (CG == 2) {
+              ptx::st_remote_u32(const_cast<int*>(&tile_q[slot]), 1, static_cast<uint32_t>(w_next));
+              ptx::mbar_arrive_remote(&qfull[slot], 1);
+            }
+            ptx::mbar_arrive(&qfull[slot]);
+          }
+          ++pub;
+          w = __shfl_sync(0xffffffffu, w_next, 0);
+          // the next number is asked for now and first looked at after this tile's loads have been issued
+          if (w >= 0 && lane == 0) w_next = atomicAdd(&g_tile_next[sched_slot], 1);
+        } else {
+          w = next_tile();
+        }
+        if (w < 0) break;
         const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
@@ -325,6 +394,13 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
       }
+      if (fetcher && lane == 0) {
+        // this unit draws no more: the last unit of the launch to say so resets the counter pair for reuse
+        if (atomicAdd(&g_tile_done[sched_slot], 1) == nunits - 1) {
+          g_tile_next[sched_slot] = 0;
+          g_tile_done[sched_slot] = 0;
+        }
+      }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ============================================
@@ -335,12 +411,13 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int w = unit; w < total_work; w += nunits) {
+      int ti = -1;
+      for (int w = next_tile(); w >= 0; w = next_tile()) {
+        ++ti;
         const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         const int kb0 = t.split * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         const bool recm = dbg != nullptr && blockIdx.x == 0 && lane == 0;
-        const int ti = (w - unit) / nunits;
         if (recm && ti < 60) {
           dbg[1024 + 4 * ti] = clock64();                              // tile start
           unsigned long long gt;
@@ -357,7 +434,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
           if (recm) waited += clock64() - w0;
-          if (w == unit && kb == kb0) gstamp_if(lane == 0, 4);          // first operands landed
+          if (ti == 0 && kb == kb0) gstamp_if(lane == 0, 4);            // first operands landed
           const uint32_t a_addr = ptx::smem_u32(smem_a + stage * A_BYTES);
           const uint32_t b_addr = ptx::smem_u32(smem_b + stage * B_BYTES);
           // K-major:  rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused (1).
@@ -406,7 +483,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
     } else if (!tma_epi) {
       // ---- direct-store fallback (outputs whose row stride is not a multiple of 16 bytes) ----
       const bool use_atomics = (ep.kind == NSB_EPI_ACCUM) && splits > 1;
-      for (int w = unit; w < total_work; w += nunits) {
+      for (int w = next_tile(); w >= 0; w = next_tile()) {
         const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         ptx::mbar_wait(&tfull[as], aphase);
         ptx::tc_fence_after();
@@ -457,7 +534,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       auto unit_col = [&](int u) -> int {             // first column (within the tile) of unit u
         return c32 ? (grp + u * ngroups) * 32 : (grp + (u >> 1) * ngroups) * 64 + (u & 1) * 32;
       };
-      for (int w = unit; w < total_work; w += nunits) {
+      for (int w = next_tile(); w >= 0; w = next_tile()) {
         const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
         const uint32_t tbase = tmem_base + lane_bits + static_cast<uint32_t>(as * BN);
@@ -579,7 +656,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         ptx::mbar_arrive(&stgbar[emit % nbuf]);
         ++emit;
       };
-      for (int w = unit; w < total_work; w += nunits) {
+      for (int w = next_tile(); w >= 0; w = next_tile()) {
         const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         ptx::mbar_wait(&tfull[as], aphase);
         ptx::tc_fence_after();
@@ -751,50 +828,71 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       const int EPC = (ep.kind == NSB_EPI_GELU) ? 2 : 1;    // emissions per chunk
       const bool aux_tma = (ep.kind == NSB_EPI_RESIDUAL || ep.kind == NSB_EPI_DGELU) && !aux_direct;
       const bool reduce = (ep.kind == NSB_EPI_ACCUM) && (ep.accumulate || splits > 1);
-      const int my_tiles = (total_work - unit + nunits - 1) / nunits;
-      const int total_chunks = my_tiles * CHG;
-      const int total_emit = total_chunks * EPC;
       uint8_t* pool = smem_stg + grp * nbuf * STG_BYTES;
       uint64_t* auxbar = auxfull + grp * nbuf;
       uint64_t* stgbar = staged + grp * nbuf;
       uint64_t* freebar = freeb + grp * nbuf;
-      auto coords = [&](int chunk, int& col, int& rowg) {
-        const TileCoord t = tile_of(unit + (chunk / CHG) * nunits, num_m, num_n, n_fast);
+      // This warp runs ahead of its group (aux tiles are requested nbuf chunks early, possibly in a later
+      // tile), so it keeps the tile numbers it has read so far; tile_at(i) = i-th tile of this CTA or -1.
+      int tl[8];
+      int fetched = 0;
+      bool exhausted = false;
+      auto tile_at = [&](int seq) -> int {          // whole warp
+        while (fetched <= seq && !exhausted) {
+          const int w = next_tile();
+          if (w < 0) exhausted = true;
+          else { tl[fetched & 7] = w; ++fetched; }
+        }
+        return seq < fetched ? tl[seq & 7] : -1;
+      };
+      auto coords = [&](int w, int chunk, int& col, int& rowg) {
+        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
         col = t.n_blk * BN + ((chunk % CHG) * ngroups + grp) * CW;
         rowg = (t.m_blk * CG + static_cast<int>(rank)) * BM;
       };
-      auto load_aux = [&](int chunk) {       // elected lane only
+      auto load_aux = [&](int w, int chunk) {       // elected lane only
         int col, rowg;
-        coords(chunk, col, rowg);
+        coords(w, chunk, col, rowg);
         const int b = chunk % nbuf;
         ptx::mbar_expect_tx(&auxbar[b], STG_BYTES);
         ptx::tma_load_2d(pool + b * STG_BYTES, &tma_aux, &auxbar[b], col, rowg);
       };
-      if (aux_tma && ptx::elect_one()) {
-        for (int j = 0; j < nbuf && j < total_chunks; ++j) load_aux(j);
+      if (aux_tma) {
+        for (int j = 0; j < nbuf; ++j) {
+          const int w = tile_at(j / CHG);
+          if (w < 0) break;
+          if (ptx::elect_one()) load_aux(w, j);
+          __syncwarp();
+        }
       }
-      __syncwarp();
       // stores allowed to be still reading their buffer; with aux tiles a buffer is refilled as early as
       // possible (the refill is the look-ahead of the aux stream: nbuf - inflight chunks)
       const int inflight = aux_tma ? (nbuf >= 6 ? 2 : 1) : (nbuf > 4 ? 2 : nbuf - 2);
-      for (int e = 0; e < total_emit; ++e) {
+      for (int e = 0;; ++e) {
+        const int chunk = e / EPC;
+        const int w = tile_at(chunk / CHG);
+        if (w < 0) break;
         const int b = e % nbuf;
         ptx::mbar_wait(&stgbar[b], (e / nbuf) & 1);
         if (ptx::elect_one()) {
           int col, rowg;
-          coords(e / EPC, col, rowg);
+          coords(w, chunk, col, rowg);
           const CUtensorMap* map = (EPC == 2 && (e & 1)) ? &tma_c2 : &tma_c;
           if (reduce) ptx::tma_reduce_add_2d(map, pool + b * STG_BYTES, col, rowg);
           else ptx::tma_store_2d(map, pool + b * STG_BYTES, col, rowg);
           ptx::bulk_commit();
-          if (e >= inflight) {
-            if (inflight <= 0) ptx::bulk_wait_read<0>(); else if (inflight == 1) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<2>();
-            const int done = e - inflight;    // this emission's buffer has been read out
-            if (aux_tma) { if (done + nbuf < total_chunks) load_aux(done + nbuf); }
-            else ptx::mbar_arrive(&freebar[done % nbuf]);
-          }
         }
         __syncwarp();
+        if (e >= inflight) {
+          const int done = e - inflight;      // this emission's buffer has been read out once the wait below returns
+          const int w_ahead = aux_tma ? tile_at((done + nbuf) / CHG) : -1;   // (aux epilogues emit once per chunk)
+          if (ptx::elect_one()) {
+            if (inflight <= 0) ptx::bulk_wait_read<0>(); else if (inflight == 1) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<2>();
+            if (aux_tma) { if (w_ahead >= 0) load_aux(w_ahead, done + nbuf); }
+            else ptx::mbar_arrive(&freebar[done % nbuf]);
+          }
+          __syncwarp();
+        }
       }
       if (ptx::elect_one()) ptx::bulk_wait_read<0>();   // smem may be released once the stores have read it
       __syncwarp();
@@ -881,6 +979,8 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint
 }
 
 static long long* g_gemm_dbg = nullptr;
+static std::atomic<unsigned> g_sched_seq{0};
+static int g_dynamic_sched = 1;
 static int g_force_nbuf = 0, g_force_stages = 0, g_pipe_epi = 1;   // debug: staging buffers per group / operand ring depth
 struct LaunchPlan {
   CUtensorMap ta, tb, tc, tc2, taux;
@@ -897,6 +997,8 @@ static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_
   }
   const size_t smem = smem_bytes_for(BN / CG, lp.stages, lp.nbuf * lp.ngroups);
   const int total = lp.num_m * lp.num_n * lp.splits;
+  // dynamic tile scheduling (g_dynamic_sched, default on): this launch's counter pair; -1 = static walk
+  const int sched_slot = g_dynamic_sched ? static_cast<int>(g_sched_seq.fetch_add(1, std::memory_order_relaxed) % kSchedSlots) : -1;
   const int units = sm_count() / CG;
   const int grid = (total < units ? total : units) * CG;
   cudaLaunchConfig_t cfg{};
@@ -914,7 +1016,7 @@ static int launch_variant(const LaunchPlan& lp, const EpiParams& ep, cudaStream_
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, lp.ta, lp.tb, lp.tc, lp.tc2, lp.taux, lp.K, lp.num_m, lp.num_n, lp.splits,
-                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, lp.n_fast, lp.pipe_epi, ep, g_gemm_dbg);
+                                     lp.kb_per_split, lp.stages, lp.nbuf, lp.tma_epi, lp.ngroups, lp.aux_direct, lp.n_fast, lp.pipe_epi, sched_slot, ep, g_gemm_dbg);
   NSB_REQUIRE(e == cudaSuccess, "gemm_tc: launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("gemm_tc");
@@ -1068,6 +1170,8 @@ void nsb_gemm_debug_pipeline(int nbuf, int stages, int pipe_epi) {
   nsb::g_force_stages = stages;
   if (pipe_epi >= 0) nsb::g_pipe_epi = pipe_epi;
 }
+// 1 (default): tiles are drawn from a per-launch counter by the CTAs that are running; 0: fixed stride walk
+void nsb_gemm_debug_scheduler(int dynamic) { nsb::g_dynamic_sched = dynamic != 0; }
 void nsb_gemm_debug_timing(void* device_buffer) { nsb::g_gemm_dbg = static_cast<long long*>(device_buffer); }
 
 int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {

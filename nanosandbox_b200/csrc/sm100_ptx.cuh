@@ -138,6 +138,39 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank)
       ::"r"(smem_u32(bar)), "r"(rank)
       : "memory");
 }
+// 32-bit store into the same smem offset of CTA `rank` of the cluster (distributed shared memory)
+__device__ __forceinline__ void st_remote_u32(void* p, uint32_t rank, uint32_t v) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "st.shared::cluster.b32 [ra], %2;\n\t}"
+      ::"r"(smem_u32(p)), "r"(rank), "r"(v)
+      : "memory");
+}
+// Wait that also acquires at cluster scope: pairs with mbar_arrive_remote (release.cluster) when the
+// arriving thread of ANOTHER CTA wrote ordinary shared-memory data for the waiter before arriving.
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait_cluster(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait_cluster(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {
+      printf("nsb: mbarrier (cluster) timeout block %d thread %d bar %u parity %u\n", blockIdx.x, threadIdx.x,
+             smem_u32(bar), parity);
+      __trap();
+    }
+  }
+}
 // TMA load issued by either CTA of a pair; the transaction bytes are credited to the LEADER's
 // mbarrier (peer bit cleared), the data lands in the issuing CTA's own shared memory
 __device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {

@@ -380,6 +380,47 @@ def test_gemm_tc_tile_walk_orders(walk, epi, a_k, b_k, M, N, K):
         lib.nsb_gemm_debug_config(0, 0, 0)
 
 
+@pytest.mark.parametrize("epi,a_k,b_k,M,N,K", [
+    (_lib.EPI_STORE, True, True, 8192, 1024, 128),
+    (_lib.EPI_RESIDUAL, True, True, 4000, 1160, 192),
+    (_lib.EPI_DGELU, True, False, 3000, 1000, 192),
+    (_lib.EPI_ACCUM, False, False, 2304, 768, 2048),
+])
+def test_gemm_tc_static_tile_walk(epi, a_k, b_k, M, N, K):
+    """The fixed-stride tile walk (A/B switch) gives the same results as the default tile counter."""
+    lib = _lib.load()
+    lib.nsb_gemm_debug_scheduler(0)
+    try:
+        _gemm_case(torch.bfloat16, M, N, K, a_k, b_k, epi, accumulate=True, alpha=0.5)
+    finally:
+        lib.nsb_gemm_debug_scheduler(1)
+
+
+def test_gemm_tc_tile_counters_are_recycled():
+    """More launches than there are tile counters (1024), on two streams at once: every launch must find its
+    counter back at zero, i.e. still compute every tile exactly once."""
+    torch.manual_seed(3)
+    M, N, K = 1024, 768, 256
+    A = (torch.randn(M, K, device=DEV) / 16).to(torch.bfloat16)
+    Bm = torch.randn(N, K, device=DEV).to(torch.bfloat16)
+    ref = (A.float() @ Bm.float().t())
+    side = torch.cuda.Stream()
+    outs = [torch.zeros(M, N, device=DEV) for _ in range(2)]
+    acc = [torch.zeros(M, N, device=DEV) for _ in range(2)]
+    torch.cuda.synchronize()
+    n = 1300
+    for i in range(n):
+        ops.gemm(M, N, K, A, K, True, Bm, K, True, outs[0], N)
+        ops.gemm(M, N, K, A, K, True, Bm, K, True, acc[0], N, _lib.EPI_ACCUM, accumulate=True)
+        with torch.cuda.stream(side):
+            ops.gemm(M, N, K, A, K, True, Bm, K, True, outs[1], N)
+            ops.gemm(M, N, K, A, K, True, Bm, K, True, acc[1], N, _lib.EPI_ACCUM, accumulate=True)
+    torch.cuda.synchronize()
+    for j in range(2):
+        assert_close(outs[j], ref, 1e-2, "last store")
+        assert_close(acc[j], ref * n, 1e-2, "sum over all launches")   # a lost or repeated tile shows up here
+
+
 def test_gemm_tc_matches_simt_path():
     """The tcgen05 kernel against our own exact SIMT kernel on identical bf16 inputs."""
     torch.manual_seed(7)

@@ -127,7 +127,8 @@ HEADLINE = {
 @pytest.mark.parametrize("name", list(HEADLINE))
 def test_bf16_headline_configs_match_oracle(name):
     """One bf16 training forward/backward at the benchmarked shapes against the oracle model run with stock
-    torch CUDA ops on the same inputs: loss 2e-2 (and within 0.2 of ln V at init), every gradient 2e-2."""
+    torch CUDA ops on the same inputs: loss 2e-2 (and near ln V at init: within 0.2, 0.35 for the 1024-wide
+    model whose initial logits have more variance), every gradient 2e-2."""
     kw, B = HEADLINE[name]
     ref, ours = build_pair(False, **kw)
     ours.to(DEV)
@@ -142,7 +143,7 @@ def test_bf16_headline_configs_match_oracle(name):
     rloss.backward()
     oloss.backward()
     torch.cuda.synchronize()
-    assert abs(oloss.item() - math.log(V)) < 0.2, (oloss.item(), math.log(V))
+    assert abs(oloss.item() - math.log(V)) < (0.35 if kw["n_embd"] > 768 else 0.2), (oloss.item(), math.log(V))
     assert abs(oloss.item() - rloss.item()) < 2e-2 * abs(rloss.item())
     for (n1, p1), (_, p2) in zip(ref.named_parameters(), ours.named_parameters()):
         e = rel(p2.grad, p1.grad)

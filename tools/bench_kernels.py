@@ -20,6 +20,9 @@ def timeit(fn, iters=10, warm=3):
     ts = []
     for _ in range(iters):
         flush.zero_()
+        # keep the GPU busy (~100 us spin) while the host enqueues event, kernel, event: the interval then holds
+        # the kernel and not the host's launch path (ctypes for ours, the ATen dispatcher for torch)
+        torch.cuda._sleep(200_000)
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(); fn(); b.record()
         torch.cuda.synchronize()
@@ -45,14 +48,29 @@ def gemm_row(name, M, N, K, a_k, b_k, epi=_lib.EPI_STORE, accumulate=False):
     print(f"{name:28s} {M:6d}x{N:6d}x{K:6d} ours {t*1e3:8.1f} us {fl/t/1e9:7.1f} TF/s ({fl/t/1e9/PEAKS['bf16_tflops']*100:5.1f}% of measured) | cuBLAS {t_ref*1e3:8.1f} us {fl/t_ref/1e9:7.1f} TF/s", flush=True)
 
 
+def clocks():
+    import subprocess
+    try:
+        return subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active",
+                               "--format=csv,noheader"], capture_output=True, text=True, timeout=20).stdout.strip()
+    except Exception as exc:
+        return f"nvidia-smi unavailable ({exc})"
+
+
 def main():
     Mt, Cc, V = 12288, 768, 50304
+    print(f"# {torch.cuda.get_device_name(0)}; torch {torch.__version__}; clocks before: {clocks()}")
+    print("# every row: median of 10, L2 flushed before each iteration, same process; cuBLAS = torch.matmul on the same operands "
+          "(plain product, no epilogue)")
     E = _lib
     gemm_row("qkv fwd", Mt, 3 * Cc, Cc, True, True)
     gemm_row("attn proj fwd (+res)", Mt, Cc, Cc, True, True, E.EPI_RESIDUAL)
+    gemm_row("fc fwd (store)", Mt, 4 * Cc, Cc, True, True)
     gemm_row("fc fwd (+gelu)", Mt, 4 * Cc, Cc, True, True, E.EPI_GELU)
     gemm_row("mlp proj fwd (+res)", Mt, Cc, 4 * Cc, True, True, E.EPI_RESIDUAL)
     gemm_row("lm_head fwd", Mt, V, Cc, True, True)
+    gemm_row("attn proj dgrad", Mt, Cc, Cc, True, False)
+    gemm_row("mlp proj dgrad (store)", Mt, 4 * Cc, Cc, True, False)
     gemm_row("mlp proj dgrad (+dgelu)", Mt, 4 * Cc, Cc, True, False, E.EPI_DGELU)
     gemm_row("fc dgrad", Mt, Cc, 4 * Cc, True, False)
     gemm_row("qkv dgrad", Mt, Cc, 3 * Cc, True, False)
@@ -63,6 +81,9 @@ def main():
     gemm_row("mlp proj wgrad", Cc, 4 * Cc, Mt, False, False, E.EPI_ACCUM, True)
     gemm_row("lm_head wgrad", V, Cc, Mt, False, False, E.EPI_ACCUM, True)
 
+    print(f"# clocks after the GEMM rows: {clocks()}")
+    if "--gemm-only" in sys.argv:
+        return
     # attention
     B, T, H, D = 12, 1024, 12, 64
     qkv = torch.randn(B, T, 3 * Cc, device=DEV).to(torch.bfloat16)
