@@ -168,6 +168,28 @@ int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const floa
                       void* dqkv, float* delta, float* dq_acc, int dtype, int B, int T, int H, int D,
                       nsb_stream_t stream);
 
+/* ---- dropout (config.dropout > 0: nanoGPT's shakespeare_char recipe trains with 0.2) -----------------------
+ * Masks are not stored: an element is kept when its word of Philox4x32-10(key = seed, counter = (element
+ * index / 4, stream_id)) is >= floor(p * 2^32), so forward and backward regenerate the same mask from the same
+ * (seed, stream_id).  Kept values are scaled by 1 / (1 - p). */
+
+/* nn.Dropout (torch/nn/functional.py: dropout) on a flat tensor of n elements, optionally fused with the
+ * residual add that follows it in Block.forward: y = (residual ? residual : 0) + dropout(x).  x / y: f32 or
+ * bf16 (y must be f32 when a residual is given); in place (y == x) is allowed.  Used for transformer.drop,
+ * attn.resid_dropout and mlp.dropout, and with the same (seed, stream_id) on the incoming gradient in backward. */
+int nsb_dropout(const void* x, int x_dtype, const float* residual, void* y, int y_dtype, size_t n, float p,
+                unsigned long long seed, unsigned long long stream_id, nsb_stream_t stream);
+
+/* K4 with F.scaled_dot_product_attention's dropout_p: the mask index of probability (b, h, q, k) is
+ * ((b H + h) T + q) T + k.  The softmax normaliser is that of the undropped probabilities, as in torch.
+ * Exact SIMT kernels (any head dim, f32 or bf16). */
+int nsb_attention_fwd_dropout(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H, int D,
+                              float p, unsigned long long seed, unsigned long long stream_id,
+                              nsb_stream_t stream);
+int nsb_attention_bwd_dropout(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
+                              float* delta, int dtype, int B, int T, int H, int D, float p,
+                              unsigned long long seed, unsigned long long stream_id, nsb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

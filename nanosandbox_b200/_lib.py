@@ -31,7 +31,7 @@ class GemmArgs(C.Structure):
     ]
 
 
-_P, _I, _F, _Z = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+_P, _I, _F, _Z, _U64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_ulonglong
 
 # name -> (restype, argtypes); every symbol include/nanosandbox_b200.h declares
 SIGNATURES = {
@@ -59,6 +59,9 @@ SIGNATURES = {
     "nsb_gemm": (_I, [C.POINTER(GemmArgs), _P]),
     "nsb_attention_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "nsb_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "nsb_dropout": (_I, [_P, _I, _P, _P, _I, _Z, _F, _U64, _U64, _P]),
+    "nsb_attention_fwd_dropout": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _F, _U64, _U64, _P]),
+    "nsb_attention_bwd_dropout": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _F, _U64, _U64, _P]),
 }
 # test / tuning hooks exported by the library but not part of the reference-facing surface
 DEBUG_SIGNATURES = {

@@ -6,6 +6,7 @@
 //    query block): deterministic, no atomics.
 //  * attn_*_simt kernels: exact fp32 math for the 1e-5 parity mode and for head dims != 64.
 #include "common.cuh"
+#include "philox.cuh"
 
 namespace nsb {
 
@@ -19,10 +20,34 @@ template <typename T> __device__ __forceinline__ void stf(T* p, float v);
 template <> __device__ __forceinline__ void stf<float>(float* p, float v) { *p = v; }
 template <> __device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 
-template <typename T, int DPL>
+// Dropout on the attention probabilities (F.scaled_dot_product_attention(dropout_p=...)): element (b, h, q, k)
+// of the [B, H, T, T] probability tensor has linear index e = ((b H + h) T + q) T + k and is kept when word
+// e % 4 of philox4x32_10(seed, e / 4, stream) is >= thr (philox.cuh).  The softmax normaliser uses the
+// undropped probabilities; kept ones are scaled by 1 / (1 - p).
+struct DropArgs { unsigned long long seed, stream; uint32_t thr; float inv_keep; };
+
+// Random words of 32 consecutive Philox counters held across the lanes of a warp: word(e) for the elements
+// e of the counters [cbase, cbase + 32).  All lanes call get() with the same e.
+struct WarpPhilox {
+  long long cbase = -1;
+  uint32_t w[4];
+  __device__ __forceinline__ uint32_t get(unsigned long long e, const DropArgs& d, int lane) {
+    const long long c = static_cast<long long>(e >> 2);
+    if (cbase < 0 || c < cbase || c - cbase >= 32) {
+      cbase = c;
+      const Philox4 r = philox4x32_10(d.seed, static_cast<unsigned long long>(c) + lane, d.stream);
+      w[0] = r.w[0]; w[1] = r.w[1]; w[2] = r.w[2]; w[3] = r.w[3];
+    }
+    const int k = static_cast<int>(e & 3);
+    const uint32_t mine = k == 0 ? w[0] : (k == 1 ? w[1] : (k == 2 ? w[2] : w[3]));
+    return __shfl_sync(0xffffffffu, mine, static_cast<int>(c - cbase));
+  }
+};
+
+template <typename T, int DPL, bool DROP>
 __global__ void __launch_bounds__(256)
     attn_fwd_simt(const T* __restrict__ qkv, T* __restrict__ y, float* __restrict__ lse, int B, int Tn,
-                  int H, float scale) {
+                  int H, float scale, DropArgs drop) {
   const int D = DPL * 32, C = H * D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long r = static_cast<long long>(blockIdx.x) * 8 + warp;
@@ -33,6 +58,8 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
   for (int i = 0; i < DPL; ++i) { qv[i] = ldf(base + static_cast<size_t>(q) * 3 * C + lane + 32 * i); o[i] = 0.f; }
   float m = -INFINITY, l = 0.f;
+  WarpPhilox rng;
+  const unsigned long long erow = static_cast<unsigned long long>(r) * static_cast<unsigned long long>(Tn);
   for (int j = 0; j <= q; ++j) {
     const T* kp = base + static_cast<size_t>(j) * 3 * C + C;
     const T* vp = kp + C;
@@ -42,8 +69,10 @@ __global__ void __launch_bounds__(256)
     s = warp_sum(s) * scale;
     const float mn = fmaxf(m, s), corr = expf(m - mn), p = expf(s - mn);
     l = l * corr + p;
+    float pd = p;
+    if (DROP) pd = rng.get(erow + j, drop, lane) >= drop.thr ? p * drop.inv_keep : 0.f;
 #pragma unroll
-    for (int i = 0; i < DPL; ++i) o[i] = o[i] * corr + p * ldf(vp + lane + 32 * i);
+    for (int i = 0; i < DPL; ++i) o[i] = o[i] * corr + pd * ldf(vp + lane + 32 * i);
     m = mn;
   }
   const float inv = 1.f / l;
@@ -68,10 +97,11 @@ __global__ void __launch_bounds__(256)
   if (lane == 0) delta[(static_cast<size_t>(b) * H + h) * Tn + q] = s;
 }
 
-template <typename T, int DPL>
+template <typename T, int DPL, bool DROP>
 __global__ void __launch_bounds__(256)
     attn_bwd_dq_simt(const T* __restrict__ qkv, const T* __restrict__ dy, const float* __restrict__ lse,
-                     const float* __restrict__ delta, T* __restrict__ dqkv, int B, int Tn, int H, float scale) {
+                     const float* __restrict__ delta, T* __restrict__ dqkv, int B, int Tn, int H, float scale,
+                     DropArgs drop) {
   const int D = DPL * 32, C = H * D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long r = static_cast<long long>(blockIdx.x) * 8 + warp;
@@ -88,6 +118,8 @@ __global__ void __launch_bounds__(256)
     dov[i] = ldf(dy + yoff + lane + 32 * i);
     dq[i] = 0.f;
   }
+  WarpPhilox rng;
+  const unsigned long long erow = static_cast<unsigned long long>(r) * static_cast<unsigned long long>(Tn);
   for (int j = 0; j <= q; ++j) {
     const T* kp = base + static_cast<size_t>(j) * 3 * C + C;
     const T* vp = kp + C;
@@ -101,6 +133,7 @@ __global__ void __launch_bounds__(256)
     }
     s = warp_sum(s) * scale;
     dp = warp_sum(dp);
+    if (DROP) dp = rng.get(erow + j, drop, lane) >= drop.thr ? dp * drop.inv_keep : 0.f;   // gradient through the mask
     const float ds = expf(s - L) * (dp - dl) * scale;
 #pragma unroll
     for (int i = 0; i < DPL; ++i) dq[i] += ds * kv[i];
@@ -110,10 +143,11 @@ __global__ void __launch_bounds__(256)
     stf(dqkv + (static_cast<size_t>(b) * Tn + q) * 3 * C + h * D + lane + 32 * i, dq[i]);
 }
 
-template <typename T, int DPL>
+template <typename T, int DPL, bool DROP>
 __global__ void __launch_bounds__(256)
     attn_bwd_dkv_simt(const T* __restrict__ qkv, const T* __restrict__ dy, const float* __restrict__ lse,
-                      const float* __restrict__ delta, T* __restrict__ dqkv, int B, int Tn, int H, float scale) {
+                      const float* __restrict__ delta, T* __restrict__ dqkv, int B, int Tn, int H, float scale,
+                      DropArgs drop) {
   const int D = DPL * 32, C = H * D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long r = static_cast<long long>(blockIdx.x) * 8 + warp;
@@ -127,6 +161,10 @@ __global__ void __launch_bounds__(256)
     vv[i] = ldf(base + static_cast<size_t>(j) * 3 * C + 2 * C + lane + 32 * i);
     dk[i] = dv[i] = 0.f;
   }
+  // masks of this key column for 32 queries at a time: lane L holds the word of query q0 + L
+  const unsigned long long ehead = (static_cast<unsigned long long>(r) / Tn) * Tn;   // (b H + h) T
+  int q0 = -1;
+  uint32_t word = 0;
   for (int q = j; q < Tn; ++q) {
     const size_t so = (static_cast<size_t>(b) * H + h) * Tn + q;
     const size_t yoff = (static_cast<size_t>(b) * Tn + q) * C + h * D;
@@ -142,9 +180,22 @@ __global__ void __launch_bounds__(256)
     s = warp_sum(s) * scale;
     dp = warp_sum(dp);
     const float p = expf(s - lse[so]);
+    float pd = p;
+    if (DROP) {
+      if (q0 < 0 || q - q0 >= 32) {
+        q0 = q;
+        const unsigned long long e = (ehead + static_cast<unsigned long long>(q0 + lane)) * Tn + j;
+        const Philox4 rr = philox4x32_10(drop.seed, e >> 2, drop.stream);
+        const int k = static_cast<int>(e & 3);
+        word = k == 0 ? rr.w[0] : (k == 1 ? rr.w[1] : (k == 2 ? rr.w[2] : rr.w[3]));
+      }
+      const bool keep = __shfl_sync(0xffffffffu, word, q - q0) >= drop.thr;
+      pd = keep ? p * drop.inv_keep : 0.f;
+      dp = keep ? dp * drop.inv_keep : 0.f;
+    }
     const float ds = p * (dp - delta[so]) * scale;
 #pragma unroll
-    for (int i = 0; i < DPL; ++i) { dv[i] += p * dov[i]; dk[i] += ds * qv[i]; }
+    for (int i = 0; i < DPL; ++i) { dv[i] += pd * dov[i]; dk[i] += ds * qv[i]; }
   }
 #pragma unroll
   for (int i = 0; i < DPL; ++i) {
@@ -555,6 +606,49 @@ void attention_tc_set_bwd_warps16(int on);
 void attention_tc_set_fwd_p_tmem(int on);
 int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
                             float* delta, float* dq_acc, int B, int T, int H, cudaStream_t stream);
+
+// ---- launchers of the exact SIMT kernels (drop == nullptr: no dropout) -----------------------------------
+int attention_fwd_simt_launch(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H, int D,
+                              const DropArgs* drop, cudaStream_t stream) {
+  const float scale = 1.0f / sqrtf(static_cast<float>(D));
+  const long long rows = static_cast<long long>(B) * H * T;
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  const DropArgs d = drop ? *drop : DropArgs{0, 0, 0, 1.f};
+#define ATT_FWD(TT, DPL)                                                                                                  \
+  do {                                                                                                                    \
+    if (drop) attn_fwd_simt<TT, DPL, true><<<grid, 256, 0, stream>>>(static_cast<const TT*>(qkv), static_cast<TT*>(y), lse, B, T, H, scale, d); \
+    else attn_fwd_simt<TT, DPL, false><<<grid, 256, 0, stream>>>(static_cast<const TT*>(qkv), static_cast<TT*>(y), lse, B, T, H, scale, d);     \
+  } while (0)
+  if (dtype == NSB_F32) { switch (D / 32) { case 1: ATT_FWD(float, 1); break; case 2: ATT_FWD(float, 2); break; case 3: ATT_FWD(float, 3); break; default: ATT_FWD(float, 4); } }
+  else { switch (D / 32) { case 1: ATT_FWD(__nv_bfloat16, 1); break; case 2: ATT_FWD(__nv_bfloat16, 2); break; case 3: ATT_FWD(__nv_bfloat16, 3); break; default: ATT_FWD(__nv_bfloat16, 4); } }
+#undef ATT_FWD
+  count_launch();
+  return check_launch("attention_fwd");
+}
+
+// delta must already hold sum_d dy * y
+int attention_bwd_simt_launch(const void* qkv, const void* dy, const float* lse, void* dqkv, const float* delta, int dtype,
+                              int B, int T, int H, int D, const DropArgs* drop, cudaStream_t stream) {
+  const float scale = 1.0f / sqrtf(static_cast<float>(D));
+  const long long rows = static_cast<long long>(B) * H * T;
+  const unsigned rgrid = static_cast<unsigned>((rows + 7) / 8);
+  const DropArgs d = drop ? *drop : DropArgs{0, 0, 0, 1.f};
+#define ATT_BWD(TT, DPL)                                                                                                  \
+  do {                                                                                                                    \
+    if (drop) {                                                                                                           \
+      attn_bwd_dq_simt<TT, DPL, true><<<rgrid, 256, 0, stream>>>(static_cast<const TT*>(qkv), static_cast<const TT*>(dy), lse, delta, static_cast<TT*>(dqkv), B, T, H, scale, d);  \
+      attn_bwd_dkv_simt<TT, DPL, true><<<rgrid, 256, 0, stream>>>(static_cast<const TT*>(qkv), static_cast<const TT*>(dy), lse, delta, static_cast<TT*>(dqkv), B, T, H, scale, d); \
+    } else {                                                                                                              \
+      attn_bwd_dq_simt<TT, DPL, false><<<rgrid, 256, 0, stream>>>(static_cast<const TT*>(qkv), static_cast<const TT*>(dy), lse, delta, static_cast<TT*>(dqkv), B, T, H, scale, d);  \
+      attn_bwd_dkv_simt<TT, DPL, false><<<rgrid, 256, 0, stream>>>(static_cast<const TT*>(qkv), static_cast<const TT*>(dy), lse, delta, static_cast<TT*>(dqkv), B, T, H, scale, d); \
+    }                                                                                                                     \
+  } while (0)
+  if (dtype == NSB_F32) { switch (D / 32) { case 1: ATT_BWD(float, 1); break; case 2: ATT_BWD(float, 2); break; case 3: ATT_BWD(float, 3); break; default: ATT_BWD(float, 4); } }
+  else { switch (D / 32) { case 1: ATT_BWD(__nv_bfloat16, 1); break; case 2: ATT_BWD(__nv_bfloat16, 2); break; case 3: ATT_BWD(__nv_bfloat16, 3); break; default: ATT_BWD(__nv_bfloat16, 4); } }
+#undef ATT_BWD
+  count_launch(2);
+  return check_launch("attention_bwd");
+}
 }
 using namespace nsb;
 
@@ -598,14 +692,7 @@ int nsb_attention_fwd(const void* qkv, void* y, float* lse, int dtype, int B, in
     count_launch();
     return check_launch("attention_fwd");
   }
-  const long long rows = static_cast<long long>(B) * H * T;
-  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
-#define ATT_FWD(TT, DPL) attn_fwd_simt<TT, DPL><<<grid, 256, 0, cs(stream)>>>(static_cast<const TT*>(qkv), static_cast<TT*>(y), lse, B, T, H, scale)
-  if (dtype == NSB_F32) { switch (D / 32) { case 1: ATT_FWD(float, 1); break; case 2: ATT_FWD(float, 2); break; case 3: ATT_FWD(float, 3); break; default: ATT_FWD(float, 4); } }
-  else { switch (D / 32) { case 1: ATT_FWD(__nv_bfloat16, 1); break; case 2: ATT_FWD(__nv_bfloat16, 2); break; case 3: ATT_FWD(__nv_bfloat16, 3); break; default: ATT_FWD(__nv_bfloat16, 4); } }
-#undef ATT_FWD
-  count_launch();
-  return check_launch("attention_fwd");
+  return attention_fwd_simt_launch(qkv, y, lse, dtype, B, T, H, D, nullptr, cs(stream));
 }
 
 int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
@@ -645,14 +732,39 @@ int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const floa
     count_launch(2);
     return check_launch("attention_bwd");
   }
-#define ATT_BWD(TT, DPL)                                                                                          \
-  attn_bwd_dq_simt<TT, DPL><<<rgrid, 256, 0, cs(stream)>>>(static_cast<const TT*>(qkv), static_cast<const TT*>(dy), lse, delta, static_cast<TT*>(dqkv), B, T, H, scale); \
-  attn_bwd_dkv_simt<TT, DPL><<<rgrid, 256, 0, cs(stream)>>>(static_cast<const TT*>(qkv), static_cast<const TT*>(dy), lse, delta, static_cast<TT*>(dqkv), B, T, H, scale)
-  if (dtype == NSB_F32) { switch (D / 32) { case 1: ATT_BWD(float, 1); break; case 2: ATT_BWD(float, 2); break; case 3: ATT_BWD(float, 3); break; default: ATT_BWD(float, 4); } }
-  else { switch (D / 32) { case 1: ATT_BWD(__nv_bfloat16, 1); break; case 2: ATT_BWD(__nv_bfloat16, 2); break; case 3: ATT_BWD(__nv_bfloat16, 3); break; default: ATT_BWD(__nv_bfloat16, 4); } }
-#undef ATT_BWD
-  count_launch(2);
-  return check_launch("attention_bwd");
+  return attention_bwd_simt_launch(qkv, dy, lse, dqkv, delta, dtype, B, T, H, D, nullptr, cs(stream));
+}
+
+// Attention with dropout on the probabilities (training with config.dropout > 0).  Same tensors as
+// nsb_attention_fwd / _bwd; the mask is a function of (seed, stream_id) and the element's position (see
+// DropArgs), so the backward call regenerates the forward's mask from the same two numbers.  These run on
+// the exact SIMT kernels (any head dim, fp32 or bf16): a functional path, not a tuned one.
+int nsb_attention_fwd_dropout(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H, int D, float p,
+                              unsigned long long seed, unsigned long long stream_id, nsb_stream_t stream) {
+  NSB_REQUIRE(dtype == NSB_F32 || dtype == NSB_BF16, "attention_fwd_dropout: bad dtype %d", dtype);
+  NSB_REQUIRE(D % 32 == 0 && D >= 32 && D <= 128, "attention_fwd_dropout: head dim %d unsupported (32/64/96/128)", D);
+  NSB_REQUIRE(p >= 0.f && p < 1.f, "attention_fwd_dropout: p = %f is outside [0, 1)", p);
+  if (B == 0 || T == 0) return 0;
+  const DropArgs d{seed, stream_id, drop_threshold(p), 1.0f / (1.0f - p)};
+  return attention_fwd_simt_launch(qkv, y, lse, dtype, B, T, H, D, &d, cs(stream));
+}
+
+int nsb_attention_bwd_dropout(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv, float* delta,
+                              int dtype, int B, int T, int H, int D, float p, unsigned long long seed,
+                              unsigned long long stream_id, nsb_stream_t stream) {
+  NSB_REQUIRE(dtype == NSB_F32 || dtype == NSB_BF16, "attention_bwd_dropout: bad dtype %d", dtype);
+  NSB_REQUIRE(D % 32 == 0 && D >= 32 && D <= 128, "attention_bwd_dropout: head dim %d unsupported (32/64/96/128)", D);
+  NSB_REQUIRE(p >= 0.f && p < 1.f, "attention_bwd_dropout: p = %f is outside [0, 1)", p);
+  if (B == 0 || T == 0) return 0;
+  const long long rows = static_cast<long long>(B) * H * T;
+  const unsigned rgrid = static_cast<unsigned>((rows + 7) / 8);
+  if (dtype == NSB_F32)
+    attn_delta_kernel<float><<<rgrid, 256, 0, cs(stream)>>>(static_cast<const float*>(y), static_cast<const float*>(dy), delta, B, T, H, D);
+  else
+    attn_delta_kernel<__nv_bfloat16><<<rgrid, 256, 0, cs(stream)>>>(static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H, D);
+  count_launch();
+  const DropArgs d{seed, stream_id, drop_threshold(p), 1.0f / (1.0f - p)};
+  return attention_bwd_simt_launch(qkv, dy, lse, dqkv, delta, dtype, B, T, H, D, &d, cs(stream));
 }
 
 }  // extern "C"

@@ -323,10 +323,14 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
     }
     const int slot = q_seq & (kTileQ - 1);
     const uint32_t ph = static_cast<uint32_t>(q_seq / kTileQ) & 1u;
-    if (CG == 2) ptx::mbar_wait_cluster(&qfull[slot], ph); else ptx::mbar_wait(&qfull[slot], ph);
+    // peer CTA of a pair: the entry arrives as an asynchronous store that completes 4 bytes on qfull; the
+    // peer's producer (a reader of every entry, in order) arms the barrier for it
+    if (CG == 2 && rank == 1 && warp == 0 && lane == 0) ptx::mbar_expect_tx(&qfull[slot], 4);
+    ptx::mbar_wait(&qfull[slot], ph);
     const int w = tile_q[slot];
     __syncwarp();
-    if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&qempty[slot], 0); else ptx::mbar_arrive(&qempty[slot]); }
+    // (w >= -1 always holds: the test makes the arrive wait for the value, i.e. the slot is released after the read)
+    if (lane == 0 && w >= -1) { if (CG == 2) ptx::mbar_arrive_remote_cta(&qempty[slot], 0); else ptx::mbar_arrive(&qempty[slot]); }
     ++q_seq;
     return w;
   };
@@ -348,13 +352,10 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
           if (lane == 0) {
             if (w_next >= total_work) w_next = -1;
             const int slot = pub & (kTileQ - 1);
-            const uint32_t qph = (static_cast<uint32_t>(pub / kTileQ) & 1u) ^ 1u;
-            if (CG == 2) ptx::mbar_wait_cluster(&qempty[slot], qph); else ptx::mbar_wait(&qempty[slot], qph);
+            ptx::mbar_wait(&qempty[slot], (static_cast<uint32_t>(pub / kTileQ) & 1u) ^ 1u);
             tile_q[slot] = w_next;
-            if (CG == 2) {
-              ptx::st_remote_u32(const_cast<int*>(&tile_q[slot]), 1, static_cast<uint32_t>(w_next));
-              ptx::mbar_arrive_remote(&qfull[slot], 1);
-            }
+            if (CG == 2)
+              ptx::st_async_remote_u32(const_cast<int*>(&tile_q[slot]), &qfull[slot], 1, static_cast<uint32_t>(w_next));
             ptx::mbar_arrive(&qfull[slot]);
           }
           ++pub;
@@ -495,7 +496,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         }
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
+        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote_cta(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     } else if (pipe_epi && ep.kind != NSB_EPI_GELU && ep.kind != NSB_EPI_DGELU) {
@@ -620,7 +621,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
             // every accumulator of this tile is in registers: hand the TMEM buffer back before staging
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
+            if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote_cta(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
           }
           process(u + 1, y);
         }
@@ -809,7 +810,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         }
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
+        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote_cta(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
       gstamp(6);                                                        // last chunk staged

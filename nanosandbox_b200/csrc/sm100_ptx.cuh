@@ -138,6 +138,29 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank)
       ::"r"(smem_u32(bar)), "r"(rank)
       : "memory");
 }
+// The same arrive with the default (CTA-scope) release: enough when nothing but the arrival itself has to
+// cross to the other CTA -- tensor-memory reads are ordered by tcgen05.fence::before_thread_sync, data sent
+// with st.async completes on the barrier by itself.  The cluster-scope form above costs a MEMBAR.ALL.GPU.
+__device__ __forceinline__ void mbar_arrive_remote_cta(uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(smem_u32(bar)), "r"(rank)
+      : "memory");
+}
+// Asynchronous 32-bit store into CTA `rank`'s shared memory that completes 4 transaction bytes on that
+// CTA's mbarrier (both given by their local addresses): data and signal travel together, the receiver
+// needs no cluster-scope acquire.
+__device__ __forceinline__ void st_async_remote_u32(void* p, uint64_t* bar, uint32_t rank, uint32_t v) {
+  asm volatile(
+      "{\n\t.reg .b32 ra, rb;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %2;\n\t"
+      "mapa.shared::cluster.u32 rb, %1, %2;\n\t"
+      "st.async.shared::cluster.mbarrier::complete_tx::bytes.u32 [ra], %3, [rb];\n\t}"
+      ::"r"(smem_u32(p)), "r"(smem_u32(bar)), "r"(rank), "r"(v)
+      : "memory");
+}
 // 32-bit store into the same smem offset of CTA `rank` of the cluster (distributed shared memory)
 __device__ __forceinline__ void st_remote_u32(void* p, uint32_t rank, uint32_t v) {
   asm volatile(

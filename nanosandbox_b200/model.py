@@ -105,6 +105,15 @@ class _Acts:
         self.B, self.T, self.M, self.lowp, self.adt = B, T, M, lowp, adt
         self.train = train
         self.gen = 0            # bumped by every forward that overwrites these buffers
+        self.drop = None        # (p, seed, first stream id) of the forward that filled these buffers, or None
+        self.proj_tmp = None    # c_proj output before dropout + residual add (allocated on first use)
+        self.dmask = None       # masked copy of the residual gradient (operand of the c_proj gradient GEMMs)
+        self._cfg_c, self._device = C, device
+
+    def dropout_buffers(self):
+        if self.proj_tmp is None:
+            self.proj_tmp = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
+            self.dmask = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
         self.x = [new(M, C, dtype=f32) for _ in range(L + 1)]       # residual stream, block inputs
         self.xmid = [new(M, C, dtype=f32) for _ in range(L)]         # after attention
         self.ln1 = [new(M, C) for _ in range(L)]
@@ -200,6 +209,7 @@ class GPT(nn.Module):
         self._arena: ParamArena | None = None
         self._acts = {}
         self._infer_acts = None
+        self._dropout_calls = 0
         self._step_logits = None
         self._grad_sync = None          # set by nanosandbox_b200.ddp.DistributedDataParallel
         # bf16 path: GELU as its own memory-bound kernels (faster on B200 than the fused GEMM epilogues,
@@ -378,9 +388,6 @@ class GPT(nn.Module):
         b, t = idx.size()
         assert t <= self.config.block_size, \
             f"Cannot forward sequence of length {t}, block size is only {self.config.block_size}"
-        if self.training and self.config.dropout != 0.0:
-            raise NotImplementedError("dropout > 0 is not implemented in the fused path yet "
-                                      "(pass --dropout=0.0, as the reference's own runs do)")
         if targets is not None and torch.is_grad_enabled() and self.lm_head.weight.requires_grad:
             loss = _FusedStep.apply(self.lm_head.weight, self, idx, targets)
             logits, self._step_logits = self._step_logits, None
@@ -439,17 +446,43 @@ class GPT(nn.Module):
         W = lambda n: arena.w(n, lowp)
         P = arena.p
         bias = (lambda n: P(n)) if cfg.bias else (lambda n: None)
+        # dropout (training mode, config.dropout > 0): the four nn.Dropout sites of nanoGPT.  Masks are Philox
+        # functions of (seed, stream id, element); every site of every forward gets its own stream id, which
+        # backward reuses.  The seed is the CUDA generator's (torch.manual_seed sets it, per rank in train.py).
+        pdrop = float(cfg.dropout) if (self.training and cfg.dropout > 0.0) else 0.0
+        if pdrop > 0.0:
+            a.dropout_buffers()
+            a.drop = (pdrop, torch.cuda.initial_seed() & ((1 << 63) - 1), self._dropout_calls * (3 * L + 1))
+            self._dropout_calls += 1
+        else:
+            a.drop = None
+        seed, sid0 = (a.drop[1], a.drop[2]) if a.drop else (0, 0)
+
+        def proj_residual(l, x_in, k_in, wname, res, out, site):
+            # out = res + dropout(x_in @ W^T + b): the residual epilogue when there is no dropout, else the
+            # GEMM stores its result and the dropout kernel does the add
+            if a.drop is None:
+                ops.gemm(M, C, k_in, x_in, k_in, True, W(wname + ".weight"), k_in, True, out, C,
+                         EPI_RESIDUAL, aux=res, bias=bias(wname + ".bias"), stream=st)
+            else:
+                ops.gemm(M, C, k_in, x_in, k_in, True, W(wname + ".weight"), k_in, True, a.proj_tmp, C,
+                         EPI_STORE, bias=bias(wname + ".bias"), stream=st)
+                ops.dropout(a.proj_tmp, out, pdrop, seed, sid0 + site + 3 * l, residual=res, stream=st)
 
         ops.embedding_fwd(idx, P("transformer.wte.weight"), P("transformer.wpe.weight"), a.x[0], st)
+        if a.drop:
+            ops.dropout(a.x[0], a.x[0], pdrop, seed, sid0, stream=st)
         for l in range(L):
             pre = f"transformer.h.{l}."
             s = a.stat[l]
             ops.layernorm_fwd(a.x[l], P(pre + "ln_1.weight"), bias(pre + "ln_1.bias"), a.ln1[l], s[0], s[1], 1e-5, st)
             ops.gemm(M, 3 * C, C, a.ln1[l], C, True, W(pre + "attn.c_attn.weight"), C, True, a.qkv[l], 3 * C,
                      EPI_STORE, bias=bias(pre + "attn.c_attn.bias"), stream=st)
-            ops.attention_fwd(a.qkv[l], a.att[l], a.lse[l], B, T, H, D, st)
-            ops.gemm(M, C, C, a.att[l], C, True, W(pre + "attn.c_proj.weight"), C, True, a.xmid[l], C,
-                     EPI_RESIDUAL, aux=a.x[l], bias=bias(pre + "attn.c_proj.bias"), stream=st)
+            if a.drop:
+                ops.attention_fwd_dropout(a.qkv[l], a.att[l], a.lse[l], B, T, H, D, pdrop, seed, sid0 + 1 + 3 * l, st)
+            else:
+                ops.attention_fwd(a.qkv[l], a.att[l], a.lse[l], B, T, H, D, st)
+            proj_residual(l, a.att[l], C, pre + "attn.c_proj", a.x[l], a.xmid[l], 2)
             ops.layernorm_fwd(a.xmid[l], P(pre + "ln_2.weight"), bias(pre + "ln_2.bias"), a.ln2[l], s[2], s[3], 1e-5, st)
             if lowp and self.split_gelu:
                 ops.gemm(M, 4 * C, C, a.ln2[l], C, True, W(pre + "mlp.c_fc.weight"), C, True, a.fch[l], 4 * C,
@@ -458,8 +491,7 @@ class GPT(nn.Module):
             else:
                 ops.gemm(M, 4 * C, C, a.ln2[l], C, True, W(pre + "mlp.c_fc.weight"), C, True, a.fch[l], 4 * C,
                          EPI_GELU, C2=a.fca[l], bias=bias(pre + "mlp.c_fc.bias"), stream=st)
-            ops.gemm(M, C, 4 * C, a.fca[l], 4 * C, True, W(pre + "mlp.c_proj.weight"), 4 * C, True, a.x[l + 1], C,
-                     EPI_RESIDUAL, aux=a.xmid[l], bias=bias(pre + "mlp.c_proj.bias"), stream=st)
+            proj_residual(l, a.fca[l], 4 * C, pre + "mlp.c_proj", a.xmid[l], a.x[l + 1], 3)
         ops.layernorm_fwd(a.x[L], P("transformer.ln_f.weight"), bias("transformer.ln_f.bias"), a.lnf,
                           a.statf[0], a.statf[1], 1e-5, st)
         wte = W("transformer.wte.weight")
@@ -501,6 +533,7 @@ class GPT(nn.Module):
         has_bias = cfg.bias
         sync = self._grad_sync
         act = (lambda t32, tl: tl) if lowp else (lambda t32, tl: t32)
+        drop = a.drop
 
         main = torch.cuda.current_stream()
         side = None
@@ -552,8 +585,13 @@ class GPT(nn.Module):
             pre = f"transformer.h.{l}."
             s = a.stat[l]
             dres, dres_a = a.dres[cur], act(a.dres[cur], a.dres_lowp)
+            rd = "dres"
+            if drop:      # gradient through mlp.dropout: the c_proj GEMMs see the masked copy
+                before_overwrite("dmask")
+                ops.dropout(dres, a.dmask, drop[0], drop[1], drop[2] + 3 + 3 * l, stream=st)
+                dres_a, rd = a.dmask, "dmask"
             # MLP
-            wgrad(dres_a, C, a.fca[l], 4 * C, pre + "mlp.c_proj", C, 4 * C, reads="dres")
+            wgrad(dres_a, C, a.fca[l], 4 * C, pre + "mlp.c_proj", C, 4 * C, reads=rd)
             before_overwrite("dh")
             if lowp and self.split_gelu:
                 ops.gemm(M, 4 * C, C, dres_a, C, True, W(pre + "mlp.c_proj.weight"), 4 * C, False, a.dh, 4 * C,
@@ -570,11 +608,20 @@ class GPT(nn.Module):
                               True, a.ln_scratch, st)
             cur ^= 1
             dres, dres_a = a.dres[cur], act(a.dres[cur], a.dres_lowp)
+            rd = "dres"
+            if drop:      # gradient through attn.resid_dropout
+                before_overwrite("dmask")
+                ops.dropout(dres, a.dmask, drop[0], drop[1], drop[2] + 2 + 3 * l, stream=st)
+                dres_a, rd = a.dmask, "dmask"
             # attention
-            wgrad(dres_a, C, a.att[l], C, pre + "attn.c_proj", C, C, reads="dres")
+            wgrad(dres_a, C, a.att[l], C, pre + "attn.c_proj", C, C, reads=rd)
             ops.gemm(M, C, C, dres_a, C, True, W(pre + "attn.c_proj.weight"), C, False, a.datt, C, EPI_STORE, stream=st)
             before_overwrite("dqkv")
-            ops.attention_bwd(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D, a.dq_acc, st)
+            if drop:
+                ops.attention_bwd_dropout(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D,
+                                          drop[0], drop[1], drop[2] + 1 + 3 * l, st)
+            else:
+                ops.attention_bwd(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D, a.dq_acc, st)
             wgrad(a.dqkv, 3 * C, a.ln1[l], C, pre + "attn.c_attn", 3 * C, C, reads="dqkv")
             ops.gemm(M, C, 3 * C, a.dqkv, 3 * C, True, W(pre + "attn.c_attn.weight"), C, False, a.dln, C, EPI_STORE, stream=st)
             before_overwrite("dres")
@@ -587,6 +634,8 @@ class GPT(nn.Module):
             if sync is not None:
                 sync.bucket_ready(i)
         join_side()                  # wte: lm_head weight gradient before the embedding scatter; also the final join
+        if drop:                     # gradient through transformer.drop
+            ops.dropout(a.dres[cur], a.dres[cur], drop[0], drop[1], drop[2], stream=st)
         ops.embedding_bwd(a.idx, a.dres[cur], G("transformer.wte.weight"), G("transformer.wpe.weight"), True, st)
         if sync is not None:
             sync.bucket_ready(L)

@@ -173,5 +173,26 @@ def attention_bwd(qkv, y, dy, lse, dqkv, delta, B, T, H, D, dq_acc=None, stream=
                                         stream or stream_handle()), "attention_bwd")
 
 
+def dropout(x, y, p, seed, stream_id, residual=None, stream=None):
+    """y = (residual or 0) + dropout(x), mask = f(seed, stream_id, element index); y may be x (in place)."""
+    _require_cuda(x, "x")
+    check(_lib.load().nsb_dropout(x.data_ptr(), dtype_code(x), ptr(residual), y.data_ptr(), dtype_code(y), x.numel(),
+                                  float(p), int(seed), int(stream_id), stream or stream_handle()), "dropout")
+    return y
+
+
+def attention_fwd_dropout(qkv, y, lse, B, T, H, D, p, seed, stream_id, stream=None):
+    _require_cuda(qkv, "qkv")
+    check(_lib.load().nsb_attention_fwd_dropout(qkv.data_ptr(), y.data_ptr(), lse.data_ptr(), dtype_code(qkv), B, T, H, D,
+                                                float(p), int(seed), int(stream_id), stream or stream_handle()),
+          "attention_fwd_dropout")
+
+
+def attention_bwd_dropout(qkv, y, dy, lse, dqkv, delta, B, T, H, D, p, seed, stream_id, stream=None):
+    check(_lib.load().nsb_attention_bwd_dropout(qkv.data_ptr(), y.data_ptr(), dy.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
+                                                delta.data_ptr(), dtype_code(qkv), B, T, H, D, float(p), int(seed),
+                                                int(stream_id), stream or stream_handle()), "attention_bwd_dropout")
+
+
 def launch_count() -> int:
     return int(_lib.load().nsb_launch_count())

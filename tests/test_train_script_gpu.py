@@ -63,6 +63,18 @@ def test_single_gpu_train_eval_checkpoint_resume(tmp_path):
     assert losses(out3)
 
 
+def test_char_recipe_with_its_default_dropout(tmp_path):
+    """config/train_shakespeare_char.py as shipped (dropout = 0.2, the recipe both reference runs start from):
+    trains, evaluates without dropout, and learns the Markov stream."""
+    prepare(tmp_path)
+    common = [a for a in COMMON if not a.startswith("--dropout")]
+    out = run([sys.executable, "train.py", *common, "--max_iters=60", "--out_dir=out_drop"], tmp_path)
+    ls = losses(out)
+    assert ls[-1] < ls[0] - 0.3, ls
+    ev = [float(m) for m in re.findall(r"step \d+: train loss ([0-9.]+)", out)]
+    assert ev and ev[-1] < ev[0] - 0.3, ev      # evaluation loss (model.eval(): no dropout) falls as well
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_torchrun_two_ranks(tmp_path):
     prepare(tmp_path)
