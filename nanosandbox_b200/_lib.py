@@ -75,6 +75,7 @@ DEBUG_SIGNATURES = {
 }
 
 _lib = None
+GEMM_SCHED_MODE = "auto"
 
 
 def load() -> C.CDLL:
@@ -96,8 +97,12 @@ def load() -> C.CDLL:
         lib.nsb_attention_debug_config(int(os.environ["NSB_ATTN_MODE"]))
     if os.environ.get("NSB_GEMM_PDL", "1") == "0":  # A/B switch for the dependent-launch overlap
         lib.nsb_gemm_debug_pdl(0)
-    if os.environ.get("NSB_GEMM_DYNAMIC", "1") == "0":  # A/B switch: fixed-stride tile walk instead of the tile counter
-        lib.nsb_gemm_debug_scheduler(0)
+    # GEMM tile scheduling: "auto" (default) = fixed-stride walk, switched to the per-launch tile counter by the
+    # model while a gradient all-reduce shares the GPU with backward (see GPT._engine_backward); "1" / "0" pin
+    # the tile counter / the fixed walk for a whole run
+    global GEMM_SCHED_MODE
+    GEMM_SCHED_MODE = os.environ.get("NSB_GEMM_DYNAMIC", "auto")
+    lib.nsb_gemm_debug_scheduler(1 if GEMM_SCHED_MODE == "1" else 0)
     _lib = lib
     return lib
 

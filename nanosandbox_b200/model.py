@@ -109,11 +109,6 @@ class _Acts:
         self.proj_tmp = None    # c_proj output before dropout + residual add (allocated on first use)
         self.dmask = None       # masked copy of the residual gradient (operand of the c_proj gradient GEMMs)
         self._cfg_c, self._device = C, device
-
-    def dropout_buffers(self):
-        if self.proj_tmp is None:
-            self.proj_tmp = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
-            self.dmask = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
         self.x = [new(M, C, dtype=f32) for _ in range(L + 1)]       # residual stream, block inputs
         self.xmid = [new(M, C, dtype=f32) for _ in range(L)]         # after attention
         self.ln1 = [new(M, C) for _ in range(L)]
@@ -150,6 +145,11 @@ class _Acts:
         # fp32 dQ accumulator of the tensor-core attention backward (kept all-zero between calls)
         self.dq_acc = torch.zeros(M, C, dtype=f32, device=device) if (lowp and C // H == 64) else None
         self.ln_scratch = torch.empty(ops.layernorm_bwd_scratch_bytes(M, C) // 4, dtype=f32, device=device)
+
+    def dropout_buffers(self):
+        if self.proj_tmp is None:
+            self.proj_tmp = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
+            self.dmask = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
 
 
 class _FusedStep(torch.autograd.Function):
@@ -535,6 +535,11 @@ class GPT(nn.Module):
         act = (lambda t32, tl: tl) if lowp else (lambda t32, tl: t32)
         drop = a.drop
 
+        # the gradient all-reduce of this backward will share the GPU with it: let the GEMMs' running CTAs absorb
+        # the tiles of CTAs that find their SM taken (dynamic tile counter) until the buckets are joined
+        overlapped_comm = sync is not None and getattr(sync, "require_backward_grad_sync", True)
+        if overlapped_comm:
+            ops.gemm_dynamic_tiles(True)
         main = torch.cuda.current_stream()
         side = None
         if self.overlap_wgrad:
@@ -640,3 +645,5 @@ class GPT(nn.Module):
         if sync is not None:
             sync.bucket_ready(L)
             sync.finish_backward()
+        if overlapped_comm:
+            ops.gemm_dynamic_tiles(False)

@@ -194,5 +194,14 @@ def attention_bwd_dropout(qkv, y, dy, lse, dqkv, delta, B, T, H, D, p, seed, str
                                                 int(stream_id), stream or stream_handle()), "attention_bwd_dropout")
 
 
+def gemm_dynamic_tiles(on: bool) -> None:
+    """In "auto" mode (NSB_GEMM_DYNAMIC unset): GEMM launches from now on draw their tiles from a per-launch
+    counter (on) or walk a fixed stride (off).  The counter form keeps every running CTA busy when some SMs are
+    held by another kernel (an NCCL all-reduce beside backward); the fixed walk is ~0.5 % faster when the GEMM
+    has the GPU to itself.  No effect when the environment pins one form."""
+    if _lib.GEMM_SCHED_MODE == "auto":
+        _lib.load().nsb_gemm_debug_scheduler(1 if on else 0)
+
+
 def launch_count() -> int:
     return int(_lib.load().nsb_launch_count())

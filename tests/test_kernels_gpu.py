@@ -308,11 +308,17 @@ def test_gemm_epilogues(dt, epi, bias):
 
 @pytest.mark.parametrize("epi", [_lib.EPI_STORE, _lib.EPI_GELU, _lib.EPI_RESIDUAL, _lib.EPI_DGELU, _lib.EPI_ACCUM])
 @pytest.mark.parametrize("M,N,K", [(8192, 1024, 128), (4000, 1160, 192), (2048, 2304, 64)])
-def test_gemm_tc_epilogues_many_tiles_per_cta(epi, M, N, K):
+@pytest.mark.parametrize("dynamic", [0, 1])
+def test_gemm_tc_epilogues_many_tiles_per_cta(epi, M, N, K, dynamic):
     """> 148 tiles: every CTA walks several tiles (TMEM double buffering, staging-buffer reuse and
-    the aux prefetch running ahead across tile boundaries)."""
-    _gemm_case(torch.bfloat16, M, N, K, True, True, epi, bias=epi in (_lib.EPI_STORE, _lib.EPI_GELU, _lib.EPI_RESIDUAL),
-               accumulate=True, alpha=0.75)
+    the aux prefetch running ahead across tile boundaries), under both tile schedulers."""
+    lib = _lib.load()
+    lib.nsb_gemm_debug_scheduler(dynamic)
+    try:
+        _gemm_case(torch.bfloat16, M, N, K, True, True, epi, bias=epi in (_lib.EPI_STORE, _lib.EPI_GELU, _lib.EPI_RESIDUAL),
+                   accumulate=True, alpha=0.75)
+    finally:
+        lib.nsb_gemm_debug_scheduler(1 if _lib.GEMM_SCHED_MODE == "1" else 0)
 
 
 @pytest.mark.parametrize("groups", [3, 4])
@@ -353,8 +359,17 @@ def test_gemm_wgrad_accum(dt, accumulate, M, N, K):
 # step's GEMM FLOPs.  The two gradient GEMMs read the 1.2 GB dlogits, which is what switches the tile walk
 # to n-fastest and picks the split-K plan at M = 50304; no smaller shape reaches those branches by policy.
 @pytest.mark.parametrize("which", ["fwd", "dgrad", "wgrad"])
-def test_gemm_lm_head_headline_shapes(which):
+@pytest.mark.parametrize("dynamic", [0, 1])
+def test_gemm_lm_head_headline_shapes(which, dynamic):
     T, Cc, V = 12288, 768, 50304
+    _lib.load().nsb_gemm_debug_scheduler(dynamic)
+    try:
+        _lm_head_case(which, T, Cc, V)
+    finally:
+        _lib.load().nsb_gemm_debug_scheduler(1 if _lib.GEMM_SCHED_MODE == "1" else 0)
+
+
+def _lm_head_case(which, T, Cc, V):
     if which == "fwd":       # logits[T, V] = lnf[T, C] . wte[V, C]^T
         _gemm_case(torch.bfloat16, T, V, Cc, True, True, _lib.EPI_STORE)
     elif which == "dgrad":   # dlnf[T, C] = alpha * dlogits[T, V] . wte[V, C]   (B read MN-major in place)
@@ -386,20 +401,22 @@ def test_gemm_tc_tile_walk_orders(walk, epi, a_k, b_k, M, N, K):
     (_lib.EPI_DGELU, True, False, 3000, 1000, 192),
     (_lib.EPI_ACCUM, False, False, 2304, 768, 2048),
 ])
-def test_gemm_tc_static_tile_walk(epi, a_k, b_k, M, N, K):
-    """The fixed-stride tile walk (A/B switch) gives the same results as the default tile counter."""
+def test_gemm_tc_tile_schedulers(epi, a_k, b_k, M, N, K):
+    """Both tile schedulers (0: fixed-stride walk, 1: per-launch tile counter) give the same results."""
     lib = _lib.load()
-    lib.nsb_gemm_debug_scheduler(0)
     try:
-        _gemm_case(torch.bfloat16, M, N, K, a_k, b_k, epi, accumulate=True, alpha=0.5)
+        for dynamic in (0, 1):
+            lib.nsb_gemm_debug_scheduler(dynamic)
+            _gemm_case(torch.bfloat16, M, N, K, a_k, b_k, epi, accumulate=True, alpha=0.5)
     finally:
-        lib.nsb_gemm_debug_scheduler(1)
+        lib.nsb_gemm_debug_scheduler(1 if _lib.GEMM_SCHED_MODE == "1" else 0)
 
 
 def test_gemm_tc_tile_counters_are_recycled():
     """More launches than there are tile counters (1024), on two streams at once: every launch must find its
     counter back at zero, i.e. still compute every tile exactly once."""
     torch.manual_seed(3)
+    _lib.load().nsb_gemm_debug_scheduler(1)
     M, N, K = 1024, 768, 256
     A = (torch.randn(M, K, device=DEV) / 16).to(torch.bfloat16)
     Bm = torch.randn(N, K, device=DEV).to(torch.bfloat16)
@@ -416,6 +433,7 @@ def test_gemm_tc_tile_counters_are_recycled():
             ops.gemm(M, N, K, A, K, True, Bm, K, True, outs[1], N)
             ops.gemm(M, N, K, A, K, True, Bm, K, True, acc[1], N, _lib.EPI_ACCUM, accumulate=True)
     torch.cuda.synchronize()
+    _lib.load().nsb_gemm_debug_scheduler(1 if _lib.GEMM_SCHED_MODE == "1" else 0)
     for j in range(2):
         assert_close(outs[j], ref, 1e-2, "last store")
         assert_close(acc[j], ref * n, 1e-2, "sum over all launches")   # a lost or repeated tile shows up here
