@@ -499,6 +499,127 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote_cta(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
+    } else if (pipe_epi && ep.c_bf16 && (ep.kind == NSB_EPI_GELU || ep.kind == NSB_EPI_DGELU)) {
+      // ---- bf16 GELU forward / backward epilogues, software-pipelined ------------------------
+      // Same 32-column units and two register sets as the path below.  A 64-column chunk (two units)
+      // fills one staging buffer per output: forward emits the pre-activation h and gelu(h) (two buffers,
+      // shipped through tma_c and tma_c2), backward overwrites the pre-activation tile that TMA brought
+      // into the buffer (or that the thread fetched from global, one unit ahead, when the CTA runs two
+      // groups) with dY * gelu'(h).  The math is the sigmoid form of common.cuh (gelu_sig2).
+      const bool is_fwd = ep.kind == NSB_EPI_GELU;
+      const bool aux_tma = !is_fwd && !aux_direct;
+      const bool has_bias = is_fwd && ep.bias != nullptr;
+      const bool scaled = alpha != 1.f;
+      const int UPT = BN / 32 / ngroups;              // units per tile for this group (even)
+      uint8_t* pool = smem_stg + grp * nbuf * STG_BYTES;
+      uint64_t* auxbar = auxfull + grp * nbuf;
+      uint64_t* stgbar = staged + grp * nbuf;
+      uint64_t* freebar = freeb + grp * nbuf;
+      int emit = 0;                                   // staging-buffer uses so far (buffer = emit % nbuf)
+      auto acquire = [&](int e) {
+        const int b = e % nbuf;
+        const uint32_t ph = static_cast<uint32_t>(e / nbuf) & 1u;
+        if (aux_tma) ptx::mbar_wait(&auxbar[b], ph);            // the aux tile landing doubles as "buffer free"
+        else ptx::mbar_wait(&freebar[b], ph ^ 1u);
+      };
+      auto publish = [&](int e) {
+        ptx::fence_proxy_async();
+        ptx::mbar_arrive(&stgbar[e % nbuf]);
+      };
+      const uint32_t lane_bits = static_cast<uint32_t>(q * 32) << 16;
+      auto unit_col = [&](int u) -> int { return (grp + (u >> 1) * ngroups) * 64 + (u & 1) * 32; };
+      for (int w = next_tile(); w >= 0; w = next_tile()) {
+        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
+        const int m0 = (t.m_blk * CG + static_cast<int>(rank)) * BM;
+        const uint32_t tbase = tmem_base + lane_bits + static_cast<uint32_t>(as * BN);
+        // backward without aux staging: this thread's 32 pre-activations of unit u (64 contiguous bytes)
+        auto load_h = [&](int u, uint4* hq) {
+          if (is_fwd || aux_tma) return;
+          const int n0 = t.n_blk * BN + unit_col(u);
+          const bool rok = m0 + row < ep.M;
+          const __nv_bfloat16* hp = static_cast<const __nv_bfloat16*>(ep.aux) + static_cast<size_t>(rok ? m0 + row : 0) * ep.ldc;
+          if (rok && n0 + 32 <= ep.N) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) hq[j] = __ldg(reinterpret_cast<const uint4*>(hp + n0) + j);
+          } else {
+            __nv_bfloat16 tmp[32];
+            for (int j = 0; j < 32; ++j) tmp[j] = (rok && n0 + j < ep.N) ? hp[n0 + j] : __float2bfloat16_rn(0.f);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) hq[j] = reinterpret_cast<const uint4*>(tmp)[j];
+          }
+        };
+        auto process = [&](int u, float* v, const uint4* hq) {
+          const int n0 = t.n_blk * BN + unit_col(u);
+          const int h4 = (u & 1) * 4;                 // this unit's half of the 128-byte staging rows
+          if ((u & 1) == 0) {
+            acquire(emit);
+            if (is_fwd) acquire(emit + 1);
+          }
+          uint8_t* b0 = pool + (emit % nbuf) * STG_BYTES;
+          uint8_t* b1 = pool + ((emit + 1) % nbuf) * STG_BYTES;
+          if (scaled) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= alpha;
+          }
+          if (has_bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += (n0 + j < ep.N) ? __ldg(ep.bias + n0 + j) : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (is_fwd) {
+              const uint4 hp = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                          pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+              *reinterpret_cast<uint4*>(b0 + stg_off(row, h4 + j)) = hp;
+              // gelu of the ROUNDED pre-activation (what backward and the reference see)
+              const float2 h0 = unpack_bf16x2(hp.x), h1 = unpack_bf16x2(hp.y), h2 = unpack_bf16x2(hp.z), h3 = unpack_bf16x2(hp.w);
+              const float2 g0 = gelu_sig2(h0.x, h0.y), g1 = gelu_sig2(h1.x, h1.y), g2 = gelu_sig2(h2.x, h2.y), g3 = gelu_sig2(h3.x, h3.y);
+              *reinterpret_cast<uint4*>(b1 + stg_off(row, h4 + j)) =
+                  make_uint4(pack_bf16x2(g0.x, g0.y), pack_bf16x2(g1.x, g1.y), pack_bf16x2(g2.x, g2.y), pack_bf16x2(g3.x, g3.y));
+            } else {
+              const uint4 hr = aux_tma ? *reinterpret_cast<const uint4*>(b0 + stg_off(row, h4 + j)) : hq[j];
+              const float2 h0 = unpack_bf16x2(hr.x), h1 = unpack_bf16x2(hr.y), h2 = unpack_bf16x2(hr.z), h3 = unpack_bf16x2(hr.w);
+              const float2 g0 = gelu_sig_grad_mul2(h0.x, h0.y, round_bf16(v[8 * j]), round_bf16(v[8 * j + 1]));
+              const float2 g1 = gelu_sig_grad_mul2(h1.x, h1.y, round_bf16(v[8 * j + 2]), round_bf16(v[8 * j + 3]));
+              const float2 g2 = gelu_sig_grad_mul2(h2.x, h2.y, round_bf16(v[8 * j + 4]), round_bf16(v[8 * j + 5]));
+              const float2 g3 = gelu_sig_grad_mul2(h3.x, h3.y, round_bf16(v[8 * j + 6]), round_bf16(v[8 * j + 7]));
+              *reinterpret_cast<uint4*>(b0 + stg_off(row, h4 + j)) =
+                  make_uint4(pack_bf16x2(g0.x, g0.y), pack_bf16x2(g1.x, g1.y), pack_bf16x2(g2.x, g2.y), pack_bf16x2(g3.x, g3.y));
+            }
+          }
+          if (u & 1) {
+            publish(emit);
+            if (is_fwd) publish(emit + 1);
+            emit += is_fwd ? 2 : 1;
+          }
+        };
+        ptx::mbar_wait(&tfull[as], aphase);
+        ptx::tc_fence_after();
+        float x[32], y[32];
+        uint4 hx[4], hy[4];
+        ptx::tmem_ld_32x32_async(tbase + static_cast<uint32_t>(unit_col(0)), x);
+        load_h(0, hx);
+#pragma unroll 1
+        for (int u = 0; u < UPT; u += 2) {
+          ptx::tmem_wait_ld32(x);
+          ptx::tmem_ld_32x32_async(tbase + static_cast<uint32_t>(unit_col(u + 1)), y);
+          load_h(u + 1, hy);
+          process(u, x, hx);
+          ptx::tmem_wait_ld32(y);
+          if (u + 2 < UPT) {
+            ptx::tmem_ld_32x32_async(tbase + static_cast<uint32_t>(unit_col(u + 2)), x);
+            load_h(u + 2, hx);
+          } else {
+            // every accumulator of this tile is in registers: hand the TMEM buffer back before the math
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if (CG == 2) ptx::mbar_arrive_remote_cta(&tempty[as], 0); else ptx::mbar_arrive(&tempty[as]); }
+          }
+          process(u + 1, y, hy);
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+      gstamp(6);
     } else if (pipe_epi && ep.kind != NSB_EPI_GELU && ep.kind != NSB_EPI_DGELU) {
       // ---- staged epilogue, software-pipelined (plain store / residual add / accumulation) ----
       // The tile is drained in 32-column units with two register sets: the TMEM load of unit u+1 is
@@ -1106,6 +1227,10 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   // which leaves more shared memory to the operand ring.
   lp.ngroups = ((heavy && force_groups != 1) || (tma_epi && force_groups == 2)) ? 2 : 1;
   if (ep.kind == NSB_EPI_RESIDUAL && force_groups != 2) lp.ngroups = 1;
+  // ... except behind a short mainloop (K <= 1024: attention's c_proj), where the kernel is bound by the
+  // 8 bytes / element the residual epilogue moves: two groups keep six aux / output tiles in flight instead of
+  // four (measured at 12288 x 768 x 768: 24.5 us against 31.5)
+  if (ep.kind == NSB_EPI_RESIDUAL && tma_epi && force_groups == 0 && K <= 1024) lp.ngroups = 2;
   // GELU backward with two groups reads its pre-activation tile straight from global (no room for
   // aux staging buffers next to the output buffers of two groups)
   lp.aux_direct = (ep.kind == NSB_EPI_DGELU && lp.ngroups == 2) ? 1 : 0;

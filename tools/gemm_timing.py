@@ -59,6 +59,8 @@ if ct:
     early = sorted(ct, key=lambda ic: ic[1][3])[:3]
     print("  earliest CTAs:", [(i, [x - t0 if x else 0 for x in c]) for i, c in early])
 d = [x for x in full[:1000] if x != 0]
+if not d:
+    sys.exit(0)        # this epilogue path records no per-chunk stamps
 t0 = d[0]
 rows = [d[i:i + 4] for i in range(0, len(d) - 3, 4)]
 for i, r in enumerate(rows[:int(sys.argv[7]) if len(sys.argv) > 7 else 10]):
