@@ -365,6 +365,18 @@ def main():
     h2d = accum * world * 2 * BATCH * T * 8
     d2h = 4 * world
 
+    # ---- host side of one step: how long the Python / ctypes path needs to enqueue it, GPU idle at the start
+    #      (for a step with more launches than the driver's queue holds this includes waiting for the GPU) ----
+    enq = []
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        train_step(resident, False)
+        enq.append((time.perf_counter() - t0) * 1e3)
+    torch.cuda.synchronize()
+    host = {"launches_per_step": launches / args.steps, "enqueue_ms_per_step": min(enq),
+            "device_ms_per_step": ms / args.steps}
+
     # ---- roofline of the dominant kernel (tcgen05 GEMM): CUDA events around every GEMM launch
     #      of one more step, on the launching stream ----
     peaks = load_peaks()
@@ -517,7 +529,7 @@ def main():
                     "measured_peak_tflops": peaks["tf"], "measured_sustained_tflops": peaks["tf_sus"]},
             "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": int(launches), "loss_at_init": loss0, "clocks": clocks, "roofline": roofline,
+            "gpu_launches": int(launches), "host": host, "loss_at_init": loss0, "clocks": clocks, "roofline": roofline,
             "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu,
         }
         if comm is not None:

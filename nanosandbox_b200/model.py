@@ -215,6 +215,8 @@ class GPT(nn.Module):
         # bf16 path: GELU as its own memory-bound kernels (faster on B200 than the fused GEMM epilogues,
         # whose eight epilogue warps cannot hide the erf math behind a K = 768 mainloop)
         self.split_gelu = os.environ.get("NSB_SPLIT_GELU", "1") != "0"
+        # NSB_SPLIT_GELU=fwd: forward through the fused epilogue (c_fc GEMM writes h and gelu(h)), backward split
+        self.fuse_gelu_fwd = os.environ.get("NSB_SPLIT_GELU", "1") == "fwd"
         # Training forward (bf16): the loss kernel also leaves softmax - onehot in the logits buffer (one
         # pass over the 1.2 GB of logits instead of two).  The logits no longer exist after that, so such
         # a forward returns (None, loss).  Set to False if you read the logits of a training forward.
@@ -484,7 +486,7 @@ class GPT(nn.Module):
                 ops.attention_fwd(a.qkv[l], a.att[l], a.lse[l], B, T, H, D, st)
             proj_residual(l, a.att[l], C, pre + "attn.c_proj", a.x[l], a.xmid[l], 2)
             ops.layernorm_fwd(a.xmid[l], P(pre + "ln_2.weight"), bias(pre + "ln_2.bias"), a.ln2[l], s[2], s[3], 1e-5, st)
-            if lowp and self.split_gelu:
+            if lowp and self.split_gelu and not self.fuse_gelu_fwd:
                 ops.gemm(M, 4 * C, C, a.ln2[l], C, True, W(pre + "mlp.c_fc.weight"), C, True, a.fch[l], 4 * C,
                          EPI_STORE, bias=bias(pre + "mlp.c_fc.bias"), stream=st)
                 ops.gelu_fwd(a.fch[l], a.fca[l], st)
