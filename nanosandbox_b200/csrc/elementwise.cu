@@ -277,6 +277,7 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
   }
   __syncthreads();
   const int ngroups = (M + kLnRows - 1) / kLnRows;
+  const int smask = nstages - 1, sshift = nstages == 4 ? 2 : 1;
   float4 dwacc[NV], dbacc[HAS_DB ? NV : 1];
 #pragma unroll
   for (int j = 0; j < NV; ++j) dwacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -287,8 +288,8 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
     if (lane == 0) {
       int it = 0;
       for (int g = blockIdx.x; g < ngroups; g += gridDim.x, ++it) {
-        const int s = it % nstages;
-        ptx::mbar_wait(&empty[s], ((it / nstages) & 1) ^ 1);
+        const int s = it & smask;            // nstages is 2 or 4: masks and shifts, no integer division per slab
+        ptx::mbar_wait(&empty[s], ((it >> sshift) & 1) ^ 1);
         const int row0 = g * kLnRows;
         const uint32_t rows = static_cast<uint32_t>(min(kLnRows, M - row0));
         uint8_t* st = ln_smem + static_cast<size_t>(s) * stage_bytes;
@@ -316,8 +317,8 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
     }
     for (; g < ngroups; g += gridDim.x, ++it) {
       if ((it % kLnGroups) != cg) continue;
-      const int s = it % nstages;
-      ptx::mbar_wait(&full[s], (it / nstages) & 1);
+      const int s = it & smask;
+      ptx::mbar_wait(&full[s], (it >> sshift) & 1);
       const int row = g * kLnRows + wr;
       const float mu = mu_n, rs = rs_n;
       const int gn = g + kLnGroups * gridDim.x;           // statistics of this group's next slab, one turn ahead

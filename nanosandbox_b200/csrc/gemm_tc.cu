@@ -188,18 +188,24 @@ struct TileCoord { int m_blk, n_blk, split; };
 // m-fastest walk: concurrently running tiles share the B panel, A panels stream (good when A fits
 // in L2 or is re-read few times).  n-fastest: the n-blocks of one A row-block run side by side, so
 // a huge A (the 1.2 GB dlogits in the lm_head gradient GEMMs) comes from HBM once.
+// q = a / b, r = a % b for 0 <= a < 2^22, 0 < b: one reciprocal and a correction step instead of the ~100-clock
+// integer division sequence (tile numbers are decomposed on the producer's and the store warp's critical paths)
+__device__ __forceinline__ void fast_divmod(int a, int b, int& q, int& r) {
+  if (a >= (1 << 22)) { q = a / b; r = a - q * b; return; }
+  q = __float2int_rz(__int2float_rn(a) * __frcp_rn(__int2float_rn(b)));
+  r = a - q * b;
+  if (r < 0) { r += b; --q; }
+  if (r >= b) { r -= b; ++q; }
+}
 __device__ __forceinline__ TileCoord tile_of(int w, int num_m, int num_n, int n_fast) {
   TileCoord t;
+  int rest;
   if (n_fast) {
-    t.n_blk = w % num_n;
-    const int rest = w / num_n;
-    t.m_blk = rest % num_m;
-    t.split = rest / num_m;
+    fast_divmod(w, num_n, rest, t.n_blk);
+    fast_divmod(rest, num_m, t.split, t.m_blk);
   } else {
-    t.m_blk = w % num_m;
-    const int rest = w / num_m;
-    t.n_blk = rest % num_n;
-    t.split = rest / num_n;
+    fast_divmod(w, num_m, rest, t.m_blk);
+    fast_divmod(rest, num_n, t.split, t.n_blk);
   }
   return t;
 }
@@ -415,8 +421,11 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       int ti = -1;
       for (int w = next_tile(); w >= 0; w = next_tile()) {
         ++ti;
-        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
-        const int kb0 = t.split * kb_per_split;
+        // only the split index matters here (both tile orders put it last); no integer divisions on the issue
+        // path between two tiles unless the launch is split-K
+        int split_idx = 0, rem_unused = 0;
+        if (splits > 1) fast_divmod(w, num_m * num_n, split_idx, rem_unused);
+        const int kb0 = split_idx * kb_per_split;
         const int kb1 = min(total_kb, kb0 + kb_per_split);
         const bool recm = dbg != nullptr && blockIdx.x == 0 && lane == 0;
         if (recm && ti < 60) {
@@ -515,16 +524,17 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       uint64_t* auxbar = auxfull + grp * nbuf;
       uint64_t* stgbar = staged + grp * nbuf;
       uint64_t* freebar = freeb + grp * nbuf;
-      int emit = 0;                                   // staging-buffer uses so far (buffer = emit % nbuf)
-      auto acquire = [&](int e) {
-        const int b = e % nbuf;
-        const uint32_t ph = static_cast<uint32_t>(e / nbuf) & 1u;
+      // staging buffer of the next emission and the parity of its use count, stepped (no divisions); the
+      // forward uses this buffer and the one after it
+      int eb = 0;
+      uint32_t eph = 0;
+      auto acquire = [&](int b, uint32_t ph) {
         if (aux_tma) ptx::mbar_wait(&auxbar[b], ph);            // the aux tile landing doubles as "buffer free"
         else ptx::mbar_wait(&freebar[b], ph ^ 1u);
       };
-      auto publish = [&](int e) {
+      auto publish = [&](int b) {
         ptx::fence_proxy_async();
-        ptx::mbar_arrive(&stgbar[e % nbuf]);
+        ptx::mbar_arrive(&stgbar[b]);
       };
       const uint32_t lane_bits = static_cast<uint32_t>(q * 32) << 16;
       auto unit_col = [&](int u) -> int { return (grp + (u >> 1) * ngroups) * 64 + (u & 1) * 32; };
@@ -551,12 +561,14 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         auto process = [&](int u, float* v, const uint4* hq) {
           const int n0 = t.n_blk * BN + unit_col(u);
           const int h4 = (u & 1) * 4;                 // this unit's half of the 128-byte staging rows
+          const int eb1 = (eb + 1 == nbuf) ? 0 : eb + 1;
+          const uint32_t eph1 = (eb1 == 0) ? (eph ^ 1u) : eph;
           if ((u & 1) == 0) {
-            acquire(emit);
-            if (is_fwd) acquire(emit + 1);
+            acquire(eb, eph);
+            if (is_fwd) acquire(eb1, eph1);
           }
-          uint8_t* b0 = pool + (emit % nbuf) * STG_BYTES;
-          uint8_t* b1 = pool + ((emit + 1) % nbuf) * STG_BYTES;
+          uint8_t* b0 = pool + eb * STG_BYTES;
+          uint8_t* b1 = pool + eb1 * STG_BYTES;
           if (scaled) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] *= alpha;
@@ -588,9 +600,10 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
             }
           }
           if (u & 1) {
-            publish(emit);
-            if (is_fwd) publish(emit + 1);
-            emit += is_fwd ? 2 : 1;
+            publish(eb);
+            if (is_fwd) publish(eb1);
+            for (int k = 0; k < (is_fwd ? 2 : 1); ++k)
+              if (++eb == nbuf) { eb = 0; eph ^= 1u; }
           }
         };
         ptx::mbar_wait(&tfull[as], aphase);
@@ -967,54 +980,77 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
         }
         return seq < fetched ? tl[seq & 7] : -1;
       };
-      auto coords = [&](int w, int chunk, int& col, int& rowg) {
-        const TileCoord t = tile_of(w, num_m, num_n, n_fast);
-        col = t.n_blk * BN + ((chunk % CHG) * ngroups + grp) * CW;
-        rowg = (t.m_blk * CG + static_cast<int>(rank)) * BM;
+      // tile number -> block coordinates, remembered for the last two tiles asked for (an emission and the aux
+      // look-ahead alternate between at most two tiles): the integer divisions of tile_of() stay off the
+      // per-emission path, which is what the epilogue group waits on for its next free buffer
+      int memo_w[2] = {-1, -1}, memo_m[2] = {0, 0}, memo_n[2] = {0, 0}, memo_next = 0;
+      // (w, j): tile number and chunk index within the tile (0 .. CHG-1)
+      auto coords = [&](int w, int j, int& col, int& rowg) {
+        int k = (memo_w[0] == w) ? 0 : ((memo_w[1] == w) ? 1 : -1);
+        if (k < 0) {
+          k = memo_next;
+          memo_next ^= 1;
+          const TileCoord t = tile_of(w, num_m, num_n, n_fast);
+          memo_w[k] = w; memo_m[k] = t.m_blk; memo_n[k] = t.n_blk;
+        }
+        col = memo_n[k] * BN + (j * ngroups + grp) * CW;
+        rowg = (memo_m[k] * CG + static_cast<int>(rank)) * BM;
       };
-      auto load_aux = [&](int w, int chunk) {       // elected lane only
+      auto load_aux = [&](int w, int j, int b) {     // elected lane only: aux tile of chunk j of tile w into buffer b
         int col, rowg;
-        coords(w, chunk, col, rowg);
-        const int b = chunk % nbuf;
+        coords(w, j, col, rowg);
         ptx::mbar_expect_tx(&auxbar[b], STG_BYTES);
         ptx::tma_load_2d(pool + b * STG_BYTES, &tma_aux, &auxbar[b], col, rowg);
       };
+      // Every position below is kept as a counter that is stepped, not divided: the chunk being emitted
+      // (e_seq-th tile of this CTA, chunk e_j, part e_sub of EPC, buffer e_b with parity e_ph), the aux
+      // look-ahead (la_seq, la_j, buffer la_b: chunk `emitted + nbuf`), and the oldest store still in flight.
+      int la_seq = 0, la_j = 0, la_b = 0;
       if (aux_tma) {
         for (int j = 0; j < nbuf; ++j) {
-          const int w = tile_at(j / CHG);
+          const int w = tile_at(la_seq);
           if (w < 0) break;
-          if (ptx::elect_one()) load_aux(w, j);
+          if (ptx::elect_one()) load_aux(w, la_j, la_b);
           __syncwarp();
+          if (++la_j == CHG) { la_j = 0; ++la_seq; }
+          if (++la_b == nbuf) la_b = 0;
         }
       }
       // stores allowed to be still reading their buffer; with aux tiles a buffer is refilled as early as
       // possible (the refill is the look-ahead of the aux stream: nbuf - inflight chunks)
       const int inflight = aux_tma ? (nbuf >= 6 ? 2 : 1) : (nbuf > 4 ? 2 : nbuf - 2);
+      int e_seq = 0, e_j = 0, e_sub = 0, e_b = 0, done_b = 0;
+      uint32_t e_ph = 0;
       for (int e = 0;; ++e) {
-        const int chunk = e / EPC;
-        const int w = tile_at(chunk / CHG);
+        const int w = tile_at(e_seq);
         if (w < 0) break;
-        const int b = e % nbuf;
-        ptx::mbar_wait(&stgbar[b], (e / nbuf) & 1);
+        ptx::mbar_wait(&stgbar[e_b], e_ph);
         if (ptx::elect_one()) {
           int col, rowg;
-          coords(w, chunk, col, rowg);
-          const CUtensorMap* map = (EPC == 2 && (e & 1)) ? &tma_c2 : &tma_c;
-          if (reduce) ptx::tma_reduce_add_2d(map, pool + b * STG_BYTES, col, rowg);
-          else ptx::tma_store_2d(map, pool + b * STG_BYTES, col, rowg);
+          coords(w, e_j, col, rowg);
+          const CUtensorMap* map = (e_sub == 1) ? &tma_c2 : &tma_c;
+          if (reduce) ptx::tma_reduce_add_2d(map, pool + e_b * STG_BYTES, col, rowg);
+          else ptx::tma_store_2d(map, pool + e_b * STG_BYTES, col, rowg);
           ptx::bulk_commit();
         }
         __syncwarp();
         if (e >= inflight) {
-          const int done = e - inflight;      // this emission's buffer has been read out once the wait below returns
-          const int w_ahead = aux_tma ? tile_at((done + nbuf) / CHG) : -1;   // (aux epilogues emit once per chunk)
+          // emission e - inflight (buffer done_b) has been read out once the wait below returns
+          const int w_ahead = aux_tma ? tile_at(la_seq) : -1;   // (aux epilogues emit once per chunk)
           if (ptx::elect_one()) {
             if (inflight <= 0) ptx::bulk_wait_read<0>(); else if (inflight == 1) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<2>();
-            if (aux_tma) { if (w_ahead >= 0) load_aux(w_ahead, done + nbuf); }
-            else ptx::mbar_arrive(&freebar[done % nbuf]);
+            if (aux_tma) { if (w_ahead >= 0) load_aux(w_ahead, la_j, done_b); }
+            else ptx::mbar_arrive(&freebar[done_b]);
           }
           __syncwarp();
+          if (aux_tma) { if (++la_j == CHG) { la_j = 0; ++la_seq; } }
+          if (++done_b == nbuf) done_b = 0;
         }
+        if (++e_sub == EPC) {
+          e_sub = 0;
+          if (++e_j == CHG) { e_j = 0; ++e_seq; }
+        }
+        if (++e_b == nbuf) { e_b = 0; e_ph ^= 1u; }
       }
       if (ptx::elect_one()) ptx::bulk_wait_read<0>();   // smem may be released once the stores have read it
       __syncwarp();
@@ -1234,6 +1270,8 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   // GELU backward with two groups reads its pre-activation tile straight from global (no room for
   // aux staging buffers next to the output buffers of two groups)
   lp.aux_direct = (ep.kind == NSB_EPI_DGELU && lp.ngroups == 2) ? 1 : 0;
+  // (the software-pipelined bf16 form overwrites the pre-activation tile in its staging buffer: no extra room needed)
+  if (ep.kind == NSB_EPI_DGELU && g_pipe_epi && ep.c_bf16 && tma_epi) lp.aux_direct = 0;
   lp.nbuf = tma_epi ? (lp.ngroups == 2 ? 3 : 4) : 0;
   lp.pipe_epi = g_pipe_epi;
   if (tma_epi && g_force_nbuf >= 2) lp.nbuf = g_force_nbuf;
