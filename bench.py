@@ -154,7 +154,7 @@ def cpu_reference_run(wl, world: int, n_micro: int, warmup: int):
     sample = (f"{n_micro} forward+backward micro-steps of {mb}x{T} tokens ({t_micro * 1e3:.0f} ms each) and one clip+AdamW "
               f"update ({t_opt * 1e3:.0f} ms), fp32, oracle/ restatement on stock torch CPU ops, {cores} threads; composed "
               f"as {k:.0f} micro-steps + 1 update per {tokens_per_step}-token optimizer step")
-    return tokens_per_step / step_s, step_s * 1e3, cores, sample
+    return tokens_per_step / step_s, step_s * 1e3, cores, sample, t_micro * 1e3
 
 
 def torch_gpu_baseline(dev, wl, micro_steps: int = 8):
@@ -196,19 +196,35 @@ def torch_gpu_baseline(dev, wl, micro_steps: int = 8):
                     f"{micro_steps} micro-steps per optimizer step, same GPU; informational, not the reference arm"}
 
 
+def bench_config(name, wl, world, accum, tokens_per_step, bucket_dtype):
+    """The `config` object of the result line, identical for both arms of a comparison."""
+    return {"workload": wl["label"], "parallelism": f"dp{world}", "micro_steps_per_rank": accum,
+            "tokens_per_step": tokens_per_step,
+            "l2": ("inputs larger than L2: every micro-step streams several GB of activations/weights (126 MB L2)"
+                   if name != "char" else
+                   "inputs larger than L2: one micro-step streams ~1 GB of activations (126 MB L2)"),
+            "grad_allreduce": bucket_dtype if world > 1 else "none"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     wl = WORKLOADS[args.config]
     world = max(1, args.gpus)
-    n_micro = max(1, min(args.steps, 6))
-    warm = 1 if args.warmup > 0 else 0
-    tok_s, ms, cores, sample = cpu_reference_run(wl, world, n_micro, warm)
+    n_micro = max(1, min(args.steps, 40))          # one sample is about a second of CPU work: K of them, bounded
+    warm = max(0, min(args.warmup, 5))
+    accum_total = wl["accum_total"] or world
+    T = wl["cfg"]["block_size"]
+    tok_s, composed_ms, cores, sample, micro_ms = cpu_reference_run(wl, world, n_micro, warm)
+    # a "step" of this arm is one timed sample (a forward+backward micro-step): ms_per_step is what was measured;
+    # `value` is the throughput of the full optimizer step composed from the samples (see cpu_baseline.sample)
     line = {"impl": "reference", "metric": "train_tokens_per_sec", "value": tok_s, "unit": "tokens/s",
-            "n_gpus": args.gpus, "steps": n_micro, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+            "n_gpus": args.gpus, "steps": n_micro, "warmup": warm, "ms_per_step": micro_ms,
+            "composed_optimizer_step_ms": composed_ms, "higher_is_better": True,
             "scaling": wl["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["label"]},
+            "config": bench_config(args.config, wl, world, accum_total // world, accum_total * wl["batch"] * T,
+                                   args.bucket_dtype),
             "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": tok_s, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
@@ -509,19 +525,14 @@ def main():
     if rank == 0:
         cpu = None
         if not args.no_cpu_baseline:
-            tok_s, _, cores, sample = cpu_reference_run(wl, world, 4, 1)
+            tok_s, _, cores, sample, _ = cpu_reference_run(wl, world, 4, 1)
             cpu = {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample}
         line = {
             "metric": "train_tokens_per_sec", "value": value, "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": wl["label"], "parallelism": f"dp{world}", "micro_steps_per_rank": accum,
-                       "tokens_per_step": tokens_per_step,
-                       "l2": ("inputs larger than L2: every micro-step streams several GB of activations/weights (126 MB L2)"
-                              if args.config != "char" else
-                              "inputs larger than L2: one micro-step streams ~1 GB of activations (126 MB L2)"),
-                       "grad_allreduce": args.bucket_dtype if ddp else "none"},
+            "config": bench_config(args.config, wl, world, accum, tokens_per_step, args.bucket_dtype),
             "mfu": {"flops_per_token": FLOPS_PER_TOKEN,
                     "vs_nominal_2.25PF": value * FLOPS_PER_TOKEN / (world * NOMINAL_BF16),
                     "vs_measured_peak": value * FLOPS_PER_TOKEN / (world * peaks["tf"] * 1e12),
