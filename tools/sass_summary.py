@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "nanosandbox_b200", "lib", "libnanosandbox_b200.so")
 PATTERNS = [("UTCMMA", r"\bUTC[A-Z]*MMA"), ("LDTM", r"\bLDTM"), ("STTM", r"\bSTTM"), ("UTMALDG", r"\bUTMALDG"),
             ("UTMASTG", r"\bUTMASTG"), ("UTMAREDG", r"\bUTMAREDG"), ("UBLKCP", r"\bUBLKCP"), ("SYNCS", r"\bSYNCS"),
-            ("HMMA", r"\bHMMA"), ("MUFU", r"\bMUFU"), ("ATOMG/REDG", r"\b(ATOMG|REDG|RED)\b"), ("multicast", r"MULTICAST")]
+            ("HMMA", r"\bHMMA"), ("MUFU", r"\bMUFU"), ("ATOMG/REDG", r"\b(ATOMG|REDG|RED)\b"), ("UTCBAR.MULTICAST", r"UTCBAR[.A-Z0-9_]*MULTICAST"), ("TMA-load multicast", r"(UTMALDG|UBLKCP)[.A-Z0-9_]*MULTICAST")]
 
 
 def demangle(names):
@@ -37,7 +37,7 @@ def main():
             cur = m.group(1)
             kernels[cur] = []
             continue
-        if cur is not None and re.match(r"\s+/\*[0-9a-f]{4}\*/", line):
+        if cur is not None and re.match(r"\s+/\*[0-9a-f]{4,}\*/", line):
             kernels[cur].append(line.rstrip())
     names = demangle(list(kernels))
     print(f"# cuobjdump -sass {os.path.relpath(LIB, ROOT)} ({os.path.getsize(LIB)} bytes), {len(kernels)} kernels, sm_100a")
