@@ -182,13 +182,16 @@ int nsb_dropout(const void* x, int x_dtype, const float* residual, void* y, int 
 
 /* K4 with F.scaled_dot_product_attention's dropout_p: the mask index of probability (b, h, q, k) is
  * ((b H + h) T + q) T + k.  The softmax normaliser is that of the undropped probabilities, as in torch.
- * Exact SIMT kernels (any head dim, f32 or bf16). */
+ * mask_scratch: B*H*T*T bytes of caller-owned device memory (contents need not survive the call), or NULL.
+ * bf16 with D = 64 and a scratch buffer: one element-wise pass writes the keep bytes there and the mma.sync flash
+ * kernels read them; otherwise (fp32, other head dims, no scratch) the exact SIMT kernels draw the bits themselves. */
 int nsb_attention_fwd_dropout(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H, int D,
                               float p, unsigned long long seed, unsigned long long stream_id,
-                              nsb_stream_t stream);
+                              void* mask_scratch, size_t mask_scratch_bytes, nsb_stream_t stream);
 int nsb_attention_bwd_dropout(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
                               float* delta, int dtype, int B, int T, int H, int D, float p,
-                              unsigned long long seed, unsigned long long stream_id, nsb_stream_t stream);
+                              unsigned long long seed, unsigned long long stream_id, void* mask_scratch,
+                              size_t mask_scratch_bytes, nsb_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -60,8 +60,8 @@ SIGNATURES = {
     "nsb_attention_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "nsb_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "nsb_dropout": (_I, [_P, _I, _P, _P, _I, _Z, _F, _U64, _U64, _P]),
-    "nsb_attention_fwd_dropout": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _F, _U64, _U64, _P]),
-    "nsb_attention_bwd_dropout": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _F, _U64, _U64, _P]),
+    "nsb_attention_fwd_dropout": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _F, _U64, _U64, _P, _Z, _P]),
+    "nsb_attention_bwd_dropout": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _F, _U64, _U64, _P, _Z, _P]),
 }
 # test / tuning hooks exported by the library but not part of the reference-facing surface
 DEBUG_SIGNATURES = {

@@ -204,6 +204,23 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// keep / drop bytes (1 / 0) for n elements: the same bits the exact kernels above regenerate on the fly
+// (word e % 4 of philox4x32_10(seed, e / 4, stream) >= thr), written once per attention call into a scratch
+// buffer so that the mma.sync kernels below only have to load them
+__global__ void __launch_bounds__(256)
+    dropout_mask_kernel(uint8_t* __restrict__ mask, size_t n, uint32_t thr, unsigned long long seed,
+                        unsigned long long stream) {
+  const size_t nquads = (n + 3) / 4;
+  for (size_t qd = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; qd < nquads;
+       qd += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const Philox4 r = philox4x32_10(seed, qd, stream);
+    const uint32_t bits = (r.w[0] >= thr ? 1u : 0u) | (r.w[1] >= thr ? 1u << 8 : 0u) | (r.w[2] >= thr ? 1u << 16 : 0u) |
+                          (r.w[3] >= thr ? 1u << 24 : 0u);
+    if (qd * 4 + 4 <= n) *reinterpret_cast<uint32_t*>(mask + qd * 4) = bits;
+    else for (size_t k = qd * 4; k < n; ++k) mask[k] = static_cast<uint8_t>((bits >> (8 * (k - qd * 4))) & 1u);
+  }
+}
+
 // =============================================================================================
 // bf16 tensor-core path, D = 64
 // =============================================================================================
@@ -303,7 +320,7 @@ __device__ __forceinline__ void zero_acc(float acc[8][4]) {
 // grid (ceil(T/64), B*H), 128 threads.  smem: Q | K0 V0 | K1 V1
 __global__ void __launch_bounds__(128)
     attn_fwd_mma(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ y, float* __restrict__ lse,
-                 int Tn, int H, float scale_log2) {
+                 int Tn, int H, float scale_log2, const uint8_t* __restrict__ dmask, float inv_keep) {
   using namespace fa;
   __shared__ __align__(128) uint8_t smem[5 * TILE_BYTES];
   const int C = H * 64;
@@ -375,6 +392,21 @@ __global__ void __launch_bounds__(128)
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) { o[nt][2 * r] *= corr; o[nt][2 * r + 1] *= corr; }
     }
+    if (dmask != nullptr) {
+      // dropout on the probabilities (the row sums above keep the undropped ones, as SDPA does); the 1 / (1 - p)
+      // is applied once to the output row.  keys 2 t4, 2 t4 + 1 of a row are two adjacent mask bytes
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int qq = q0 + r * 8;
+        const uint8_t* mrowp = dmask + (static_cast<size_t>(bh) * Tn + (qq < Tn ? qq : 0)) * Tn + kb * BLK + 2 * t4;
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const int key = kb * BLK + nt * 8 + 2 * t4;
+          if (key < Tn && !mrowp[nt * 8]) s[nt][2 * r] = 0.f;
+          if (key + 1 < Tn && !mrowp[nt * 8 + 1]) s[nt][2 * r + 1] = 0.f;
+        }
+      }
+    }
     uint32_t pa[4][4];
     c_to_a(pa, s);
     mma_a_bkn(o, pa, sV[cur], lane);
@@ -387,7 +419,7 @@ __global__ void __launch_bounds__(128)
     l += __shfl_xor_sync(0xffffffffu, l, 2);
     const int qq = q0 + r * 8;
     if (qq < Tn) {
-      const float inv = 1.f / l;
+      const float inv = inv_keep / l;
       __nv_bfloat16* yr = y + (static_cast<size_t>(b) * Tn + qq) * C + h * 64;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt)
@@ -401,7 +433,8 @@ __global__ void __launch_bounds__(128)
 __global__ void __launch_bounds__(128)
     attn_bwd_dkv_mma(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dy,
                      const float* __restrict__ lse, const float* __restrict__ delta,
-                     __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2) {
+                     __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2,
+                     const uint8_t* __restrict__ dmask, float inv_keep) {
   using namespace fa;
   extern __shared__ __align__(128) uint8_t smem_dyn[];
   uint8_t* smem = smem_dyn;
@@ -473,8 +506,30 @@ __global__ void __launch_bounds__(128)
         const bool live = (qq >= key) && (qq < Tn);
         s[nt][e] = live ? exp2f(s[nt][e] * scale_log2 - st[qloc]) : 0.f;
       }
+    // dropout: keep[key][q] of this thread's elements (0 / 1 / none); dV sees the dropped probabilities, the
+    // gradient through the mask scales dP, dS keeps the undropped P
+    float km[8][4];
+    if (dmask != nullptr) {
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int qq = qb * BLK + nt * 8 + 2 * t4 + (e & 1);
+          const int key = key0 + (e >> 1) * 8;
+          km[nt][e] = (qq < Tn && key < Tn && dmask[(static_cast<size_t>(bh) * Tn + qq) * Tn + key]) ? inv_keep : 0.f;
+        }
+    }
     uint32_t pa[4][4];
-    c_to_a(pa, s);
+    if (dmask != nullptr) {
+      float sd[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) sd[nt][e] = s[nt][e] * km[nt][e];
+      c_to_a(pa, sd);
+    } else {
+      c_to_a(pa, s);
+    }
     mma_a_bkn(dv, pa, sdO[cur], lane);          // dV += P^T dO
     float dp[8][4];
     zero_acc(dp);
@@ -484,7 +539,8 @@ __global__ void __launch_bounds__(128)
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const int qloc = nt * 8 + 2 * t4 + (e & 1);
-        dp[nt][e] = s[nt][e] * (dp[nt][e] - st[64 + qloc]);
+        const float dpe = dmask != nullptr ? dp[nt][e] * km[nt][e] : dp[nt][e];
+        dp[nt][e] = s[nt][e] * (dpe - st[64 + qloc]);
       }
     c_to_a(pa, dp);
     mma_a_bkn(dk, pa, sQ[cur], lane);           // dK += dS^T Q
@@ -509,7 +565,8 @@ __global__ void __launch_bounds__(128)
 __global__ void __launch_bounds__(128)
     attn_bwd_dq_mma(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dy,
                     const float* __restrict__ lse, const float* __restrict__ delta,
-                    __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2) {
+                    __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2,
+                    const uint8_t* __restrict__ dmask, float inv_keep) {
   using namespace fa;
   extern __shared__ __align__(128) uint8_t smem_dyn[];
   uint8_t* smem = smem_dyn;
@@ -573,6 +630,19 @@ __global__ void __launch_bounds__(128)
     float dp[8][4];
     zero_acc(dp);
     mma_a_bnk(dp, doa, sV[cur], lane);          // dP = dO V^T
+    if (dmask != nullptr) {                     // gradient through the dropout mask
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int qq = q0 + r * 8;
+        const uint8_t* mrowp = dmask + (static_cast<size_t>(bh) * Tn + (qq < Tn ? qq : 0)) * Tn + kb * BLK + 2 * t4;
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const int key = kb * BLK + nt * 8 + 2 * t4;
+          dp[nt][2 * r] = (key < Tn && mrowp[nt * 8]) ? dp[nt][2 * r] * inv_keep : 0.f;
+          dp[nt][2 * r + 1] = (key + 1 < Tn && mrowp[nt * 8 + 1]) ? dp[nt][2 * r + 1] * inv_keep : 0.f;
+        }
+      }
+    }
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
@@ -606,6 +676,46 @@ void attention_tc_set_bwd_warps16(int on);
 void attention_tc_set_fwd_p_tmem(int on);
 int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
                             float* delta, float* dq_acc, int B, int T, int H, cudaStream_t stream);
+
+// ---- launchers of the mma.sync flash kernels (bf16, D = 64); dmask: keep bytes [B, H, T, T] or nullptr ----------
+int attention_fwd_mma_launch(const void* qkv, void* y, float* lse, int B, int T, int H, const uint8_t* dmask,
+                             float inv_keep, cudaStream_t stream) {
+  const float scale = 1.0f / sqrtf(64.f);
+  dim3 grid((T + 63) / 64, B * H);
+  attn_fwd_mma<<<grid, 128, 0, stream>>>(static_cast<const __nv_bfloat16*>(qkv), static_cast<__nv_bfloat16*>(y), lse, T, H,
+                                         scale * 1.4426950408889634f, dmask, inv_keep);
+  count_launch();
+  return check_launch("attention_fwd");
+}
+// delta must already hold sum_d dy * y
+int attention_bwd_mma_launch(const void* qkv, const void* dy, const float* lse, const float* delta, void* dqkv, int B,
+                             int T, int H, const uint8_t* dmask, float inv_keep, cudaStream_t stream) {
+  const float scale = 1.0f / sqrtf(64.f);
+  const int smem_dkv = 6 * fa::TILE_BYTES + 2 * 128 * 4, smem_dq = 6 * fa::TILE_BYTES;
+  static PerDeviceOnce attr_done;
+  if (attr_done.first_use()) {
+    cudaFuncSetAttribute(attn_bwd_dkv_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv);
+    cudaFuncSetAttribute(attn_bwd_dq_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq);
+  }
+  dim3 grid((T + 63) / 64, B * H);
+  const float sl2 = scale * 1.4426950408889634f;
+  attn_bwd_dkv_mma<<<grid, 128, smem_dkv, stream>>>(static_cast<const __nv_bfloat16*>(qkv), static_cast<const __nv_bfloat16*>(dy),
+                                                     lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale, sl2, dmask, inv_keep);
+  attn_bwd_dq_mma<<<grid, 128, smem_dq, stream>>>(static_cast<const __nv_bfloat16*>(qkv), static_cast<const __nv_bfloat16*>(dy),
+                                                   lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale, sl2, dmask, inv_keep);
+  count_launch(2);
+  return check_launch("attention_bwd");
+}
+int attention_dropout_mask_launch(uint8_t* mask, size_t n, float p, unsigned long long seed, unsigned long long stream_id,
+                                  cudaStream_t stream) {
+  const size_t nquads = (n + 3) / 4;
+  size_t blocks = (nquads + 255) / 256;
+  const size_t cap = static_cast<size_t>(sm_count()) * 16;
+  if (blocks > cap) blocks = cap;
+  dropout_mask_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(mask, n, drop_threshold(p), seed, stream_id);
+  count_launch();
+  return check_launch("attention_dropout_mask");
+}
 
 // ---- launchers of the exact SIMT kernels (drop == nullptr: no dropout) -----------------------------------
 int attention_fwd_simt_launch(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H, int D,
@@ -686,11 +796,7 @@ int nsb_attention_fwd(const void* qkv, void* y, float* lse, int dtype, int B, in
   }
   if (dtype == NSB_BF16 && D == 64 && g_attn_force_simt == 2) {
     NSB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0, "attention_fwd: qkv must be 16-byte aligned");
-    dim3 grid((T + 63) / 64, B * H);
-    attn_fwd_mma<<<grid, 128, 0, cs(stream)>>>(static_cast<const __nv_bfloat16*>(qkv), static_cast<__nv_bfloat16*>(y),
-                                               lse, T, H, scale * 1.4426950408889634f);
-    count_launch();
-    return check_launch("attention_fwd");
+    return attention_fwd_mma_launch(qkv, y, lse, B, T, H, nullptr, 1.f, cs(stream));
   }
   return attention_fwd_simt_launch(qkv, y, lse, dtype, B, T, H, D, nullptr, cs(stream));
 }
@@ -717,41 +823,40 @@ int nsb_attention_bwd(const void* qkv, const void* y, const void* dy, const floa
   if (dtype == NSB_BF16 && D == 64 && g_attn_force_simt != 1) {
     NSB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(dy) & 15) == 0,
                 "attention_bwd: qkv/dy must be 16-byte aligned");
-    const int smem_dkv = 6 * fa::TILE_BYTES + 2 * 128 * 4, smem_dq = 6 * fa::TILE_BYTES;
-    static PerDeviceOnce attr_done;
-    if (attr_done.first_use()) {
-      cudaFuncSetAttribute(attn_bwd_dkv_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv);
-      cudaFuncSetAttribute(attn_bwd_dq_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq);
-    }
-    dim3 grid((T + 63) / 64, B * H);
-    const float sl2 = scale * 1.4426950408889634f;
-    attn_bwd_dkv_mma<<<grid, 128, smem_dkv, cs(stream)>>>(static_cast<const __nv_bfloat16*>(qkv), static_cast<const __nv_bfloat16*>(dy),
-                                                           lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale, sl2);
-    attn_bwd_dq_mma<<<grid, 128, smem_dq, cs(stream)>>>(static_cast<const __nv_bfloat16*>(qkv), static_cast<const __nv_bfloat16*>(dy),
-                                                         lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale, sl2);
-    count_launch(2);
-    return check_launch("attention_bwd");
+    return attention_bwd_mma_launch(qkv, dy, lse, delta, dqkv, B, T, H, nullptr, 1.f, cs(stream));
   }
   return attention_bwd_simt_launch(qkv, dy, lse, dqkv, delta, dtype, B, T, H, D, nullptr, cs(stream));
 }
 
 // Attention with dropout on the probabilities (training with config.dropout > 0).  Same tensors as
 // nsb_attention_fwd / _bwd; the mask is a function of (seed, stream_id) and the element's position (see
-// DropArgs), so the backward call regenerates the forward's mask from the same two numbers.  These run on
-// the exact SIMT kernels (any head dim, fp32 or bf16): a functional path, not a tuned one.
+// DropArgs), so the backward call regenerates the forward's mask from the same two numbers.  With bf16, head
+// dim 64 and a caller-provided scratch of B*H*T*T bytes the keep bytes are written there by one element-wise
+// pass and the mma.sync flash kernels read them; otherwise the exact SIMT kernels draw the bits themselves
+// (any head dim, fp32 or bf16, no scratch).
 int nsb_attention_fwd_dropout(const void* qkv, void* y, float* lse, int dtype, int B, int T, int H, int D, float p,
-                              unsigned long long seed, unsigned long long stream_id, nsb_stream_t stream) {
+                              unsigned long long seed, unsigned long long stream_id, void* mask_scratch,
+                              size_t mask_scratch_bytes, nsb_stream_t stream) {
   NSB_REQUIRE(dtype == NSB_F32 || dtype == NSB_BF16, "attention_fwd_dropout: bad dtype %d", dtype);
   NSB_REQUIRE(D % 32 == 0 && D >= 32 && D <= 128, "attention_fwd_dropout: head dim %d unsupported (32/64/96/128)", D);
   NSB_REQUIRE(p >= 0.f && p < 1.f, "attention_fwd_dropout: p = %f is outside [0, 1)", p);
   if (B == 0 || T == 0) return 0;
+  const size_t nmask = static_cast<size_t>(B) * H * T * T;
+  if (dtype == NSB_BF16 && D == 64 && mask_scratch != nullptr && mask_scratch_bytes >= nmask && g_attn_force_simt != 1 &&
+      (reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(mask_scratch) & 3) == 0) {
+    // bf16, head dim 64: keep bytes into the caller's scratch, then the mma.sync flash kernel reads them
+    const int rc = attention_dropout_mask_launch(static_cast<uint8_t*>(mask_scratch), nmask, p, seed, stream_id, cs(stream));
+    if (rc) return rc;
+    return attention_fwd_mma_launch(qkv, y, lse, B, T, H, static_cast<const uint8_t*>(mask_scratch), 1.0f / (1.0f - p), cs(stream));
+  }
   const DropArgs d{seed, stream_id, drop_threshold(p), 1.0f / (1.0f - p)};
   return attention_fwd_simt_launch(qkv, y, lse, dtype, B, T, H, D, &d, cs(stream));
 }
 
 int nsb_attention_bwd_dropout(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv, float* delta,
                               int dtype, int B, int T, int H, int D, float p, unsigned long long seed,
-                              unsigned long long stream_id, nsb_stream_t stream) {
+                              unsigned long long stream_id, void* mask_scratch, size_t mask_scratch_bytes,
+                              nsb_stream_t stream) {
   NSB_REQUIRE(dtype == NSB_F32 || dtype == NSB_BF16, "attention_bwd_dropout: bad dtype %d", dtype);
   NSB_REQUIRE(D % 32 == 0 && D >= 32 && D <= 128, "attention_bwd_dropout: head dim %d unsupported (32/64/96/128)", D);
   NSB_REQUIRE(p >= 0.f && p < 1.f, "attention_bwd_dropout: p = %f is outside [0, 1)", p);
@@ -763,6 +868,15 @@ int nsb_attention_bwd_dropout(const void* qkv, const void* y, const void* dy, co
   else
     attn_delta_kernel<__nv_bfloat16><<<rgrid, 256, 0, cs(stream)>>>(static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H, D);
   count_launch();
+  const size_t nmask = static_cast<size_t>(B) * H * T * T;
+  if (dtype == NSB_BF16 && D == 64 && mask_scratch != nullptr && mask_scratch_bytes >= nmask && g_attn_force_simt != 1 &&
+      (reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(dy) & 15) == 0 &&
+      (reinterpret_cast<uintptr_t>(mask_scratch) & 3) == 0) {
+    const int rc = attention_dropout_mask_launch(static_cast<uint8_t*>(mask_scratch), nmask, p, seed, stream_id, cs(stream));
+    if (rc) return rc;
+    return attention_bwd_mma_launch(qkv, dy, lse, delta, dqkv, B, T, H, static_cast<const uint8_t*>(mask_scratch),
+                                    1.0f / (1.0f - p), cs(stream));
+  }
   const DropArgs d{seed, stream_id, drop_threshold(p), 1.0f / (1.0f - p)};
   return attention_bwd_simt_launch(qkv, dy, lse, dqkv, delta, dtype, B, T, H, D, &d, cs(stream));
 }

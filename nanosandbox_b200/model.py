@@ -108,6 +108,7 @@ class _Acts:
         self.drop = None        # (p, seed, first stream id) of the forward that filled these buffers, or None
         self.proj_tmp = None    # c_proj output before dropout + residual add (allocated on first use)
         self.dmask = None       # masked copy of the residual gradient (operand of the c_proj gradient GEMMs)
+        self.attn_mask = None
         self._cfg_c, self._device = C, device
         self.x = [new(M, C, dtype=f32) for _ in range(L + 1)]       # residual stream, block inputs
         self.xmid = [new(M, C, dtype=f32) for _ in range(L)]         # after attention
@@ -146,10 +147,14 @@ class _Acts:
         self.dq_acc = torch.zeros(M, C, dtype=f32, device=device) if (lowp and C // H == 64) else None
         self.ln_scratch = torch.empty(ops.layernorm_bwd_scratch_bytes(M, C) // 4, dtype=f32, device=device)
 
-    def dropout_buffers(self):
+    def dropout_buffers(self, n_head):
         if self.proj_tmp is None:
             self.proj_tmp = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
             self.dmask = torch.empty(self.M, self._cfg_c, dtype=self.adt, device=self._device)
+            # keep bytes of one layer's attention probabilities [B, H, T, T]; rewritten before every use (forward
+            # and backward regenerate them), bf16 / head dim 64 only -- the exact kernels need no scratch
+            self.attn_mask = (torch.empty(self.B * n_head * self.T * self.T, dtype=torch.uint8, device=self._device)
+                              if (self.lowp and self._cfg_c // n_head == 64) else None)
 
 
 class _FusedStep(torch.autograd.Function):
@@ -453,7 +458,7 @@ class GPT(nn.Module):
         # backward reuses.  The seed is the CUDA generator's (torch.manual_seed sets it, per rank in train.py).
         pdrop = float(cfg.dropout) if (self.training and cfg.dropout > 0.0) else 0.0
         if pdrop > 0.0:
-            a.dropout_buffers()
+            a.dropout_buffers(H)
             a.drop = (pdrop, torch.cuda.initial_seed() & ((1 << 63) - 1), self._dropout_calls * (3 * L + 1))
             self._dropout_calls += 1
         else:
@@ -481,7 +486,8 @@ class GPT(nn.Module):
             ops.gemm(M, 3 * C, C, a.ln1[l], C, True, W(pre + "attn.c_attn.weight"), C, True, a.qkv[l], 3 * C,
                      EPI_STORE, bias=bias(pre + "attn.c_attn.bias"), stream=st)
             if a.drop:
-                ops.attention_fwd_dropout(a.qkv[l], a.att[l], a.lse[l], B, T, H, D, pdrop, seed, sid0 + 1 + 3 * l, st)
+                ops.attention_fwd_dropout(a.qkv[l], a.att[l], a.lse[l], B, T, H, D, pdrop, seed, sid0 + 1 + 3 * l,
+                                          a.attn_mask, st)
             else:
                 ops.attention_fwd(a.qkv[l], a.att[l], a.lse[l], B, T, H, D, st)
             proj_residual(l, a.att[l], C, pre + "attn.c_proj", a.x[l], a.xmid[l], 2)
@@ -626,7 +632,7 @@ class GPT(nn.Module):
             before_overwrite("dqkv")
             if drop:
                 ops.attention_bwd_dropout(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D,
-                                          drop[0], drop[1], drop[2] + 1 + 3 * l, st)
+                                          drop[0], drop[1], drop[2] + 1 + 3 * l, a.attn_mask, st)
             else:
                 ops.attention_bwd(a.qkv[l], a.att[l], a.datt, a.lse[l], a.dqkv, a.delta, B, T, H, D, a.dq_acc, st)
             wgrad(a.dqkv, 3 * C, a.ln1[l], C, pre + "attn.c_attn", 3 * C, C, reads="dqkv")

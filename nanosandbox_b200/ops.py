@@ -181,17 +181,21 @@ def dropout(x, y, p, seed, stream_id, residual=None, stream=None):
     return y
 
 
-def attention_fwd_dropout(qkv, y, lse, B, T, H, D, p, seed, stream_id, stream=None):
+def attention_fwd_dropout(qkv, y, lse, B, T, H, D, p, seed, stream_id, mask_scratch=None, stream=None):
+    """mask_scratch: uint8 tensor of >= B*H*T*T elements (bf16, D = 64: the mma.sync kernels) or None (exact kernels)."""
     _require_cuda(qkv, "qkv")
     check(_lib.load().nsb_attention_fwd_dropout(qkv.data_ptr(), y.data_ptr(), lse.data_ptr(), dtype_code(qkv), B, T, H, D,
-                                                float(p), int(seed), int(stream_id), stream or stream_handle()),
-          "attention_fwd_dropout")
+                                                float(p), int(seed), int(stream_id), ptr(mask_scratch),
+                                                0 if mask_scratch is None else mask_scratch.numel(),
+                                                stream or stream_handle()), "attention_fwd_dropout")
 
 
-def attention_bwd_dropout(qkv, y, dy, lse, dqkv, delta, B, T, H, D, p, seed, stream_id, stream=None):
+def attention_bwd_dropout(qkv, y, dy, lse, dqkv, delta, B, T, H, D, p, seed, stream_id, mask_scratch=None, stream=None):
     check(_lib.load().nsb_attention_bwd_dropout(qkv.data_ptr(), y.data_ptr(), dy.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
                                                 delta.data_ptr(), dtype_code(qkv), B, T, H, D, float(p), int(seed),
-                                                int(stream_id), stream or stream_handle()), "attention_bwd_dropout")
+                                                int(stream_id), ptr(mask_scratch),
+                                                0 if mask_scratch is None else mask_scratch.numel(),
+                                                stream or stream_handle()), "attention_bwd_dropout")
 
 
 def gemm_dynamic_tiles(on: bool) -> None:

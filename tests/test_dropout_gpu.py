@@ -102,9 +102,13 @@ def _attention_with_mask(qkv, B, T, H, D, mask):
     return (pr @ v).transpose(1, 2).contiguous().view(B, T, Cc)
 
 
-@pytest.mark.parametrize("dt,B,T,H,D,tol", [(torch.float32, 2, 100, 3, 32, 1e-5), (torch.float32, 1, 256, 2, 64, 1e-5),
-                                            (torch.bfloat16, 2, 130, 4, 64, 2e-2), (torch.float32, 1, 77, 2, 96, 1e-5)])
-def test_attention_dropout_matches_masked_reference(dt, B, T, H, D, tol):
+@pytest.mark.parametrize("dt,B,T,H,D,tol,scratch", [
+    (torch.float32, 2, 100, 3, 32, 1e-5, False), (torch.float32, 1, 256, 2, 64, 1e-5, False),
+    (torch.bfloat16, 2, 130, 4, 64, 2e-2, False), (torch.float32, 1, 77, 2, 96, 1e-5, False),
+    (torch.bfloat16, 2, 130, 4, 64, 2e-2, True), (torch.bfloat16, 3, 256, 6, 64, 2e-2, True), (torch.bfloat16, 1, 1000, 2, 64, 2e-2, True)])
+def test_attention_dropout_matches_masked_reference(dt, B, T, H, D, tol, scratch):
+    """scratch=False: the exact kernels draw the bits themselves; True: keep bytes into a scratch buffer, then the
+    mma.sync flash kernels (bf16, head dim 64).  Same masks either way."""
     torch.manual_seed(5)
     p, seed, sid = 0.2, 77, 11
     Cc = H * D
@@ -115,7 +119,10 @@ def test_attention_dropout_matches_masked_reference(dt, B, T, H, D, tol):
     assert abs(rate - (1 - p)) < 0.01
     y = torch.empty(B, T, Cc, device=DEV, dtype=dt)
     lse = torch.empty(B, H, T, device=DEV)
-    ops.attention_fwd_dropout(qkv, y, lse, B, T, H, D, p, seed, sid)
+    ms = torch.empty(B * H * T * T, dtype=torch.uint8, device=DEV) if scratch else None
+    ops.attention_fwd_dropout(qkv, y, lse, B, T, H, D, p, seed, sid, ms)
+    if scratch:
+        assert torch.equal(ms.view(B, H, T, T) != 0, mask != 0)          # the scratch holds exactly the keep bits
     qr = qkv.float().clone().requires_grad_(True)
     ref = _attention_with_mask(qr, B, T, H, D, mask)
     assert rel(y, ref) < tol
@@ -123,10 +130,12 @@ def test_attention_dropout_matches_masked_reference(dt, B, T, H, D, tol):
     ref.backward(dy.float())
     dqkv = torch.empty_like(qkv)
     delta = torch.empty(B, H, T, device=DEV)
-    ops.attention_bwd_dropout(qkv, y, dy, lse, dqkv, delta, B, T, H, D, p, seed, sid)
+    if scratch:
+        ms.zero_()                                                        # backward regenerates it
+    ops.attention_bwd_dropout(qkv, y, dy, lse, dqkv, delta, B, T, H, D, p, seed, sid, ms)
     assert rel(dqkv, qr.grad) < tol
     # p = 0 through the same entry points is plain attention
-    ops.attention_fwd_dropout(qkv, y, lse, B, T, H, D, 0.0, seed, sid)
+    ops.attention_fwd_dropout(qkv, y, lse, B, T, H, D, 0.0, seed, sid, ms)
     assert rel(y, _attention_with_mask(qkv.float(), B, T, H, D, torch.ones_like(mask))) < tol
 
 
