@@ -139,3 +139,23 @@ def test_from_hf_state_dict_mapping():
         a, _ = ref(idx, idx)
         b = hf(idx).logits
     assert torch.allclose(a, b, atol=1e-5, rtol=1e-5)
+
+
+def test_bench_workloads_flops_and_shared_config():
+    """bench.py's workload table: FLOPs per token = SURVEY.md 8d's figures, and both arms of a comparison emit the
+    same `config` object."""
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_module", os.path.join(root, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    assert b.flops_per_token(b.WORKLOADS["gpt2"]["cfg"]) == 854_770_176
+    assert b.flops_per_token(b.WORKLOADS["char"]["cfg"]) == 70_958_592
+    assert b.flops_per_token(b.WORKLOADS["gpt2-medium"]["cfg"]) == 2_423_298_048
+    for name, wl in b.WORKLOADS.items():
+        for world in (1, 8):
+            total = wl["accum_total"] or world
+            c = b.bench_config(name, wl, world, total // world, total * wl["batch"] * wl["cfg"]["block_size"], "bf16")
+            assert c["parallelism"] == f"dp{world}" and c["micro_steps_per_rank"] * world == total
+            assert c["grad_allreduce"] == ("bf16" if world > 1 else "none")
+    assert b.WORKLOADS["gpt2"]["accum_total"] * b.WORKLOADS["gpt2"]["batch"] * 1024 == 491_520
