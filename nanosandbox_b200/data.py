@@ -24,9 +24,16 @@ def uniform_stream(vocab_size: int, n: int = STREAM_LEN, seed: int = 0) -> np.nd
     return torch.randint(0, vocab_size, (n,), generator=g).numpy().astype(np.uint16)
 
 
-def markov_stream(vocab_size: int, n: int = 1 << 20, seed: int = 0, branching: int = 4) -> np.ndarray:
+def markov_stream(vocab_size: int, n: int = 1 << 20, seed: int = 0, branching: int = 4,
+                  chain_seed: int | None = None) -> np.ndarray:
+    """Order-1 Markov chain over the vocabulary.  chain_seed=None: transition table and walk from one generator
+    seeded with `seed` (the form the golden curves were made with); otherwise the table comes from `chain_seed`
+    and the walk from `seed`, so that a validation stream can follow the SAME chain as the training stream."""
     rng = np.random.RandomState(seed)
-    succ = rng.randint(0, vocab_size, size=(vocab_size, branching))
+    if chain_seed is None:
+        succ = rng.randint(0, vocab_size, size=(vocab_size, branching))
+    else:
+        succ = np.random.RandomState(chain_seed).randint(0, vocab_size, size=(vocab_size, branching))
     probs = np.array([0.6, 0.2, 0.15, 0.05][:branching], dtype=np.float64)
     probs /= probs.sum()
     choice = rng.choice(branching, size=n, p=probs)
@@ -46,7 +53,8 @@ def write_dataset(data_dir: str, vocab_size: int, kind: str = "uniform", n: int 
         tr, va = uniform_stream(vocab_size, n, seed), uniform_stream(vocab_size, max(n // 8, 4096), seed + 1)
     elif kind == "markov":
         n = n or (1 << 20)
-        tr, va = markov_stream(vocab_size, n, seed), markov_stream(vocab_size, max(n // 8, 4096), seed + 1)
+        tr = markov_stream(vocab_size, n, seed)
+        va = markov_stream(vocab_size, max(n // 8, 4096), seed + 1, chain_seed=seed)   # same chain, another walk
     else:
         raise ValueError(f"unknown synthetic kind {kind!r}")
     # write under temporary names and rename into place (val.bin, then meta.pkl, train.bin last: readers

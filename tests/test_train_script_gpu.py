@@ -73,6 +73,8 @@ def test_char_recipe_with_its_default_dropout(tmp_path):
     assert ls[-1] < ls[0] - 0.3, ls
     ev = [float(m) for m in re.findall(r"step \d+: train loss ([0-9.]+)", out)]
     assert ev and ev[-1] < ev[0] - 0.3, ev      # evaluation loss (model.eval(): no dropout) falls as well
+    va = [float(m) for m in re.findall(r"val loss ([0-9.]+)", out)]
+    assert va and va[-1] < va[0] - 0.3, va      # ... and on the validation stream (another walk of the same chain)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
