@@ -563,7 +563,7 @@ __global__ void __launch_bounds__(320, 2)
       // already be writing the next block's)
       float* slot = xch + (j & 1) * 256;
       slot[g * 128 + row] = mx;
-      ptx::named_bar_sync(2, 256);
+      ptx::named_bar_sync(2 + qd, 64);               // only the two warps that share these 32 rows meet
       mx = fmaxf(mx, slot[(g ^ 1) * 128 + row]);
       float corr = 1.f;
       const float m_true = mx * scale_log2;
@@ -593,7 +593,7 @@ __global__ void __launch_bounds__(320, 2)
     // total row sum, then this thread's 32 columns of O
     float* lsum = xch + 512;
     lsum[g * 128 + row] = l;
-    ptx::named_bar_sync(2, 256);
+    ptx::named_bar_sync(2 + qd, 64);
     l += lsum[(g ^ 1) * 128 + row];
     ptx::mbar_wait(o_full, 0);
     ptx::tc_fence_after();
