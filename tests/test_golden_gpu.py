@@ -83,3 +83,48 @@ def test_loss_curve_200_steps_within_one_percent(golden_dir, dtype):
     if dtype == "float32":
         psum = float(sum(p.detach().double().sum() for p in m.parameters()))
         assert abs(psum - float(c["param_sum"])) < 1e-3 * abs(float(c["param_sum"]))
+
+
+def test_loss_curve_char_config_200_steps_vs_oracle_same_gpu():
+    """BASELINE.json configs[1] (6L/6H/384, block 256, batch 64, bf16 autocast) for 200 optimizer steps on the
+    learnable Markov stream: our step against the oracle model driven by stock torch (CUDA ops, torch AdamW,
+    clip_grad_norm_) on the same GPU, same seed, same batches.  north_star: per-step losses within 1 %."""
+    from oracle.model import GPT as RefGPT, GPTConfig as RefConfig
+    kw = dict(n_layer=6, n_head=6, n_embd=384, block_size=256, vocab_size=65, bias=False, dropout=0.0)
+    stream = ndata.markov_stream(65, 1 << 18, 0)
+    steps, B, T = 200, 64, 256
+
+    def lr_at(it):
+        return get_lr(it, lr=1e-3, warm=20, decay=200, min_lr=1e-4)
+
+    def run(ours: bool):
+        torch.manual_seed(1337)
+        if ours:
+            m = GPT(GPTConfig(**kw), verbose=False).to(DEV)
+            opt = m.configure_optimizers(0.1, 1e-3, (0.9, 0.99), "cuda", verbose=False)
+        else:
+            m = RefGPT(RefConfig(**kw), verbose=False).to(DEV)
+            opt = m.configure_optimizers(0.1, 1e-3, (0.9, 0.99), "cuda", verbose=False)
+        losses = []
+        X, Y = ndata.get_batch(stream, B, T, DEV)
+        for it in range(steps):
+            for g in opt.param_groups:
+                g["lr"] = lr_at(it)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                _, loss = m(X, Y)
+            X, Y = ndata.get_batch(stream, B, T, DEV)
+            loss.backward()
+            if ours:
+                opt.clip_grad_norm_(1.0)
+            else:
+                torch.nn.utils.clip_grad_norm_(m.parameters(), 1.0)
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+            losses.append(loss.item())
+        return np.array(losses)
+
+    ref = run(False)
+    got = run(True)
+    assert ref[-1] < ref[0] - 1.0                      # the stream is learnable: the curve actually moves
+    dev = np.abs(got - ref) / ref
+    assert dev.max() < 0.01, f"max loss deviation {dev.max():.4f} at step {dev.argmax()} ({got[dev.argmax()]:.4f} vs {ref[dev.argmax()]:.4f})"
