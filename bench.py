@@ -310,20 +310,28 @@ def main():
         y = torch.stack([torch.from_numpy(data[i + 1:i + 1 + T].astype(np.int64)) for i in ix])
         return x.pin_memory(), y.pin_memory()
 
+    def next_host_batch():
+        xh, yh = host_batch()
+        return xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)
+
+    pending = [None]            # the batch fetched ahead, as nanoGPT's loop does ("prefetch the next batch")
+
     def train_step(batches, from_host: bool, sync: bool = True, update: bool = True):
-        """One optimizer step through the public API (GPT.forward / backward / clip / AdamW)."""
+        """One optimizer step through the public API (GPT.forward / backward / clip / AdamW).  from_host: the
+        loop of train.py -- every micro-step's batch is built on the host, copied from pinned memory, and the
+        NEXT one is fetched right after the forward has been enqueued, while the GPU works."""
         loss = None
+        if from_host and pending[0] is None:
+            pending[0] = next_host_batch()
         for micro in range(accum):
             if ddp:
                 model.require_backward_grad_sync = sync and (micro == accum - 1)
-            if from_host:
-                xh, yh = host_batch()
-                X, Y = xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)
-            else:
-                X, Y = batches[micro]
+            X, Y = pending[0] if from_host else batches[micro]
             with ctx:
                 _, loss = model(X, Y)
                 loss = loss / accum
+            if from_host:
+                pending[0] = next_host_batch()
             loss.backward()
         if update:
             opt.clip_grad_norm_(1.0)
