@@ -70,6 +70,7 @@ DEBUG_SIGNATURES = {
     "nsb_gemm_debug_pdl": (None, [_I]),
     "nsb_gemm_debug_pipeline": (None, [_I, _I, _I]),
     "nsb_gemm_debug_scheduler": (None, [_I]),
+    "nsb_gemm_debug_store_hint": (None, [_I]),
     "nsb_attention_debug_config": (None, [_I]),
     "nsb_attention_debug_timing": (None, [_P]),
 }
@@ -97,6 +98,8 @@ def load() -> C.CDLL:
         lib.nsb_attention_debug_config(int(os.environ["NSB_ATTN_MODE"]))
     if os.environ.get("NSB_GEMM_PDL", "1") == "0":  # A/B switch for the dependent-launch overlap
         lib.nsb_gemm_debug_pdl(0)
+    if os.environ.get("NSB_GEMM_STORE_HINT", "0") == "1":   # A/B switch: evict_first hint on stores of outputs larger than L2
+        lib.nsb_gemm_debug_store_hint(1)
     # GEMM tile scheduling: "auto" (default) = fixed-stride walk, switched to the per-launch tile counter by the
     # model while a gradient all-reduce shares the GPU with backward (see GPT._engine_backward); "1" / "0" pin
     # the tile counter / the fixed walk for a whole run

@@ -1019,6 +1019,10 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
       // stores allowed to be still reading their buffer; with aux tiles a buffer is refilled as early as
       // possible (the refill is the look-ahead of the aux stream: nbuf - inflight chunks)
       const int inflight = aux_tma ? (nbuf >= 6 ? 2 : 1) : (nbuf > 4 ? 2 : nbuf - 2);
+      // an output larger than L2 (the 1.2 GB of logits) is written with evict_first so that it does not push
+      // the operand panels, which every tile re-reads, out of L2
+      const bool stream_out = (tma_epi & 2) != 0;
+      const uint64_t evict_first = ptx::l2_policy_evict_first();
       int e_seq = 0, e_j = 0, e_sub = 0, e_b = 0, done_b = 0;
       uint32_t e_ph = 0;
       for (int e = 0;; ++e) {
@@ -1030,6 +1034,7 @@ __global__ void __launch_bounds__(64 + 160 * NGRP, 1)
           coords(w, e_j, col, rowg);
           const CUtensorMap* map = (e_sub == 1) ? &tma_c2 : &tma_c;
           if (reduce) ptx::tma_reduce_add_2d(map, pool + e_b * STG_BYTES, col, rowg);
+          else if (stream_out) ptx::tma_store_2d_hint(map, pool + e_b * STG_BYTES, col, rowg, evict_first);
           else ptx::tma_store_2d(map, pool + e_b * STG_BYTES, col, rowg);
           ptx::bulk_commit();
         }
@@ -1139,6 +1144,7 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint
 static long long* g_gemm_dbg = nullptr;
 static std::atomic<unsigned> g_sched_seq{0};
 static int g_dynamic_sched = 1;
+static int g_store_hint = 0;   // evict_first on the TMA stores of outputs larger than L2: measured no effect (lm_head forward 717-754 us either way), off
 static int g_force_nbuf = 0, g_force_stages = 0, g_pipe_epi = 1;   // debug: staging buffers per group / operand ring depth
 struct LaunchPlan {
   CUtensorMap ta, tb, tc, tc2, taux;
@@ -1250,6 +1256,9 @@ int gemm_tc_launch(const nsb_gemm_args* a, const EpiParams& ep, cudaStream_t str
   if (ep.kind == NSB_EPI_GELU) tma_epi = tma_epi && tma_ok(a->C2, cesz);
   if (has_aux) tma_epi = tma_epi && tma_ok(a->aux, ep.kind == NSB_EPI_RESIDUAL ? 4 : 2);
   lp.tma_epi = tma_epi ? 1 : 0;
+  // bit 1: the output (plain store) is larger than L2 -> stores carry the evict_first hint
+  if (tma_epi && g_store_hint && ep.kind == NSB_EPI_STORE &&
+      static_cast<double>(M) * N * cesz > 256e6) lp.tma_epi |= 2;
   lp.tc = lp.ta; lp.tc2 = lp.ta; lp.taux = lp.ta;  // placeholders when unused
   if (tma_epi) {
     const uint32_t cw = c32 ? 32 : 64;
@@ -1342,6 +1351,7 @@ void nsb_gemm_debug_pipeline(int nbuf, int stages, int pipe_epi) {
 }
 // 1 (default): tiles are drawn from a per-launch counter by the CTAs that are running; 0: fixed stride walk
 void nsb_gemm_debug_scheduler(int dynamic) { nsb::g_dynamic_sched = dynamic != 0; }
+void nsb_gemm_debug_store_hint(int on) { nsb::g_store_hint = on != 0; }
 void nsb_gemm_debug_timing(void* device_buffer) { nsb::g_gemm_dbg = static_cast<long long*>(device_buffer); }
 
 int nsb_gemm(const nsb_gemm_args* a, nsb_stream_t stream) {
