@@ -1269,14 +1269,17 @@ __global__ void __launch_bounds__(704, 1)
     const float* lse_g = lse + (static_cast<size_t>(b) * H + h) * Tn;
     const float* del_g = delta + (static_cast<size_t>(b) * H + h) * Tn;
     const int ct = threadIdx.x - 64;                // 0..511; the first 256 load the per-query statistics
+    // the statistics of the next query block are fetched one iteration ahead and only LOOKED AT (negated, log2
+    // scaling: see bwd_probs) when they are stored at the top of that iteration: any arithmetic right behind the
+    // load would park this in-order warp on the global-memory latency, and fifteen others on the barrier below
     auto load_stat = [&](int it) -> float {
       const int qg = (jb + it) * BQ + (ct & 127);
       if (ct >= 256 || qg >= Tn) return 0.f;
-      return ct < 128 ? -lse_g[qg] * 1.4426950408889634f : -del_g[qg];   // negated: see bwd_probs
+      return ct < 128 ? lse_g[qg] : del_g[qg];
     };
     float st_next = load_stat(0);
     for (int it = 0; it < nit; ++it) {
-      if (ct < 256) stat[(it & 1) * 256 + ct] = st_next;
+      if (ct < 256) stat[(it & 1) * 256 + ct] = ct < 128 ? -st_next * 1.4426950408889634f : -st_next;
       if (it + 1 < nit) st_next = load_stat(it + 1);
       ptx::named_bar_sync(3, 512);
       const float* nlse2 = stat + (it & 1) * 256 + wg * 32;
