@@ -1268,20 +1268,24 @@ __global__ void __launch_bounds__(704, 1)
     const int key = jb * BKV + row;
     const float* lse_g = lse + (static_cast<size_t>(b) * H + h) * Tn;
     const float* del_g = delta + (static_cast<size_t>(b) * H + h) * Tn;
-    const int ct = threadIdx.x - 64;                // 0..511; the first 256 load the per-query statistics
-    // the statistics of the next query block are fetched one iteration ahead and only LOOKED AT (negated, log2
-    // scaling: see bwd_probs) when they are stored at the top of that iteration: any arithmetic right behind the
-    // load would park this in-order warp on the global-memory latency, and fifteen others on the barrier below
+    // Per-query statistics (lse, delta) of a block: every group of four warps loads the 2 x 32 values of ITS
+    // 32 query columns (its first 64 threads, one value each) and meets on a barrier of its own, so the
+    // groups do not wait for one another.  The values of the next block are fetched one iteration ahead and
+    // only LOOKED AT (negated, log2 scaling: see bwd_probs) when they are stored at the top of that iteration:
+    // any arithmetic right behind the load would park this in-order warp on the global-memory latency.
+    const int gt = (threadIdx.x - 64) & 127;        // 0..127 within the group
+    const bool loader = gt < 64, is_lse = gt < 32;
+    const int scol = wg * 32 + (gt & 31);            // the query column (within the block) this thread fetches
     auto load_stat = [&](int it) -> float {
-      const int qg = (jb + it) * BQ + (ct & 127);
-      if (ct >= 256 || qg >= Tn) return 0.f;
-      return ct < 128 ? lse_g[qg] : del_g[qg];
+      const int qg = (jb + it) * BQ + scol;
+      if (!loader || qg >= Tn) return 0.f;
+      return is_lse ? lse_g[qg] : del_g[qg];
     };
     float st_next = load_stat(0);
     for (int it = 0; it < nit; ++it) {
-      if (ct < 256) stat[(it & 1) * 256 + ct] = ct < 128 ? -st_next * 1.4426950408889634f : -st_next;
+      if (loader) stat[(it & 1) * 256 + (is_lse ? 0 : 128) + scol] = is_lse ? -st_next * 1.4426950408889634f : -st_next;
       if (it + 1 < nit) st_next = load_stat(it + 1);
-      ptx::named_bar_sync(3, 512);
+      ptx::named_bar_sync(4 + wg, 128);
       const float* nlse2 = stat + (it & 1) * 256 + wg * 32;
       const float* ndlt = nlse2 + 128;
       const bool diag = (it == 0);
