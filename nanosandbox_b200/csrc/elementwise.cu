@@ -119,14 +119,22 @@ __global__ void __launch_bounds__(256)
   const int row = blockIdx.x * 8 + warp;
   if (row >= M) return;
   const float* xr = x + static_cast<size_t>(row) * C;
-  float4 v[NV];
+  float4 v[NV], wv[NV];
   float s = 0.f;
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     const int c = (lane + 32 * j) * 4;
     v[j] = (c < C) ? Vec4IO<float>::load(xr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
-    s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
   }
+  // the weights are fetched now, behind the row's own loads, not where they are used: there every one of them
+  // cost an L1 / L2 round trip with nothing else to issue (30 % of this kernel's sampled stalls)
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int c = (lane + 32 * j) * 4;
+    wv[j] = (c < C) ? __ldg(reinterpret_cast<const float4*>(w + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int j = 0; j < NV; ++j) s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
   const float mu = warp_sum(s) / static_cast<float>(C);
   float q = 0.f;
 #pragma unroll
@@ -147,9 +155,8 @@ __global__ void __launch_bounds__(256)
   for (int j = 0; j < NV; ++j) {
     const int c = (lane + 32 * j) * 4;
     if (c < C) {
-      const float4 wv = __ldg(reinterpret_cast<const float4*>(w + c));
-      float4 o = make_float4((v[j].x - mu) * rs * wv.x, (v[j].y - mu) * rs * wv.y,
-                             (v[j].z - mu) * rs * wv.z, (v[j].w - mu) * rs * wv.w);
+      float4 o = make_float4((v[j].x - mu) * rs * wv[j].x, (v[j].y - mu) * rs * wv[j].y,
+                             (v[j].z - mu) * rs * wv[j].z, (v[j].w - mu) * rs * wv[j].w);
       if (b != nullptr) {
         const float4 bv = __ldg(reinterpret_cast<const float4*>(b + c));
         o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
