@@ -276,15 +276,20 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
   const uint32_t off_x = kLnRows * dy_row, off_r = off_x + kLnRows * f_row;
   const uint32_t stage_bytes = off_r + (dres_in != nullptr ? kLnRows * f_row : 0u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(ln_smem + static_cast<size_t>(nstages) * stage_bytes);
+  // one `full` barrier per (slot, consumer group): with a ring depth that is not a multiple of kLnGroups a slot
+  // falls to the groups in turn, and a barrier that only ever serves one group cannot run a phase ahead of
+  // (or behind) the parity that group waits for -- its next phase needs that group's own release of the slot
   uint64_t* full = bars;
-  uint64_t* empty = bars + 4;
+  uint64_t* empty = bars + 4 * kLnGroups;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < nstages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], kLnRows); }
+    for (int s = 0; s < nstages; ++s) {
+      for (int q = 0; q < kLnGroups; ++q) ptx::mbar_init(&full[s * kLnGroups + q], 1);
+      ptx::mbar_init(&empty[s], kLnRows);
+    }
     ptx::fence_mbar_init();
   }
   __syncthreads();
   const int ngroups = (M + kLnRows - 1) / kLnRows;
-  const int smask = nstages - 1, sshift = nstages == 4 ? 2 : 1;
   float4 dwacc[NV], dbacc[HAS_DB ? NV : 1];
 #pragma unroll
   for (int j = 0; j < NV; ++j) dwacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -293,27 +298,27 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
 
   if (warp == kLnWarps) {
     if (lane == 0) {
-      int it = 0;
-      for (int g = blockIdx.x; g < ngroups; g += gridDim.x, ++it) {
-        const int s = it & smask;            // nstages is 2 or 4: masks and shifts, no integer division per slab
-        ptx::mbar_wait(&empty[s], ((it >> sshift) & 1) ^ 1);
+      int s = 0, q = 0;                      // ring slot, consumer group of the slab, parity of the slot's use count:
+      uint32_t ph = 0;                       // all stepped (no division per slab)
+      for (int g = blockIdx.x; g < ngroups;
+           g += gridDim.x, (++s == nstages ? (s = 0, ph ^= 1u) : 0u), (++q == kLnGroups ? (q = 0) : 0)) {
+        ptx::mbar_wait(&empty[s], ph ^ 1u);
+        uint64_t* fb = &full[s * kLnGroups + q];
         const int row0 = g * kLnRows;
         const uint32_t rows = static_cast<uint32_t>(min(kLnRows, M - row0));
         uint8_t* st = ln_smem + static_cast<size_t>(s) * stage_bytes;
-        ptx::mbar_expect_tx(&full[s], rows * (dy_row + f_row + (dres_in != nullptr ? f_row : 0u)));
-        ptx::bulk_load_1d(st, dy + static_cast<size_t>(row0) * C, rows * dy_row, &full[s]);
-        ptx::bulk_load_1d(st + off_x, x + static_cast<size_t>(row0) * C, rows * f_row, &full[s]);
+        ptx::mbar_expect_tx(fb, rows * (dy_row + f_row + (dres_in != nullptr ? f_row : 0u)));
+        ptx::bulk_load_1d(st, dy + static_cast<size_t>(row0) * C, rows * dy_row, fb);
+        ptx::bulk_load_1d(st + off_x, x + static_cast<size_t>(row0) * C, rows * f_row, fb);
         if (dres_in != nullptr)
-          ptx::bulk_load_1d(st + off_r, dres_in + static_cast<size_t>(row0) * C, rows * f_row, &full[s]);
+          ptx::bulk_load_1d(st + off_r, dres_in + static_cast<size_t>(row0) * C, rows * f_row, fb);
       }
     }
   } else {
     const float invC = 1.0f / static_cast<float>(C);
     // two groups of kLnRows warps take alternate slabs (four consumer warps per SM sub-partition hide the
-    // shared-memory and shuffle latencies of one another).  The ring depth is a multiple of kLnGroups (the
-    // launcher guarantees it), so a ring slot always belongs to the same group: a warp waits only on the
-    // slots its own group releases, the producer cannot refill such a slot before this warp has arrived
-    // on its `empty` barrier, and the parity wait below can therefore never alias a later phase.
+    // shared-memory and shuffle latencies of one another).  A warp waits only on its own group's barrier of a
+    // slot; the group comes back to the same slot every `period` of its slabs, which is when the parity flips.
     const int cg = warp / kLnRows, wr = warp % kLnRows;   // consumer group, row within the slab
     // the weight vector is the same for every row: into registers once, instead of two L1 round trips per row
     float4 wreg[NV];
@@ -322,17 +327,16 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
       const int c = (lane + 32 * j) * 4;
       wreg[j] = (c < C) ? __ldg(reinterpret_cast<const float4*>(w + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    int it = 0;
-    int g = blockIdx.x;
+    int g = blockIdx.x + cg * gridDim.x;                  // this group's first slab: the cg-th of the CTA
+    int s = cg % nstages;                                 // its ring slot
+    static_assert(kLnGroups == 2, "period below assumes two consumer groups");
+    const int period = (nstages % kLnGroups == 0) ? nstages / kLnGroups : nstages;
+    int turn = 0;                                         // slabs of this group since the parity last flipped
+    uint32_t ph = 0;
     float mu_n = 0.f, rs_n = 0.f;
-    {
-      const int g0 = g + cg * gridDim.x;                  // this group's first slab
-      if (g0 < ngroups && g0 * kLnRows + wr < M) { mu_n = mean[g0 * kLnRows + wr]; rs_n = rstd[g0 * kLnRows + wr]; }
-    }
-    for (; g < ngroups; g += gridDim.x, ++it) {
-      if ((it % kLnGroups) != cg) continue;
-      const int s = it & smask;
-      ptx::mbar_wait(&full[s], (it >> sshift) & 1);
+    if (g < ngroups && g * kLnRows + wr < M) { mu_n = mean[g * kLnRows + wr]; rs_n = rstd[g * kLnRows + wr]; }
+    for (; g < ngroups; g += kLnGroups * gridDim.x) {
+      ptx::mbar_wait(&full[s * kLnGroups + cg], ph);
       const int row = g * kLnRows + wr;
       const float mu = mu_n, rs = rs_n;
       const int gn = g + kLnGroups * gridDim.x;           // statistics of this group's next slab, one turn ahead
@@ -382,6 +386,9 @@ __global__ void __launch_bounds__(32 * (kLnWarps + 1), 1)
       }
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&empty[s]);
+      s += kLnGroups;                                     // this group's next slab is kLnGroups slots further on
+      while (s >= nstages) s -= nstages;
+      if (++turn == period) { turn = 0; ph ^= 1u; }
     }
   }
   // cross-warp reduction of the column partials (the staging ring is idle now and reused), dw then db
@@ -1111,7 +1118,6 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
   const size_t slab = kLnRows * (dy_row + static_cast<size_t>(C) * 4 * (dres_in != nullptr ? 2 : 1));
   int nstages = static_cast<int>((200 * 1024) / slab);
   if (nstages > 4) nstages = 4;
-  nstages -= nstages % kLnGroups;   // a ring slot must always fall to the same consumer group (see the kernel)
   const bool stream_ok = (dy_row % 16 == 0) && (C % 4 == 0) && nstages >= 2 && M >= 4 * kLnRows &&
                          static_cast<size_t>(nstages) * slab >= static_cast<size_t>(kLnWarps) * 128 * nv * 4;
   if (stream_ok) {
@@ -1119,7 +1125,7 @@ int layernorm_bwd_launch(const void* dy, int dy_dtype, const float* x, const flo
     if (sgrid > sm_count()) sgrid = sm_count();
     if (sgrid > grid) sgrid = grid;
     grid = sgrid;
-    const size_t smem = static_cast<size_t>(nstages) * slab + 64;
+    const size_t smem = static_cast<size_t>(nstages) * slab + 8 * (4 * kLnGroups + 4);   // ring + its mbarriers
 #define NSB_LN_BWDS(TT, HASDB)                                                                          \
   {                                                                                                     \
     auto kern = layernorm_bwd_stream_kernel<NV, TT, HASDB>;                                             \
