@@ -673,6 +673,7 @@ void attention_tc_set_dq_direct(int on);
 void attention_tc_set_kv_tmem(int on);
 void attention_tc_set_fwd_warps8(int on);
 void attention_tc_set_bwd_warps16(int on);
+void attention_tc_set_bwd_persistent(int on);
 void attention_tc_set_fwd_p_tmem(int on);
 int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, const float* lse, void* dqkv,
                             float* delta, float* dq_acc, int B, int T, int H, cudaStream_t stream);
@@ -778,6 +779,8 @@ void nsb_attention_debug_config(int force_simt) {
   if (force_simt == 12 || force_simt == 13) { attention_tc_set_bwd_warps16(force_simt == 13); g_attn_force_simt = 0; return; }
   // 14 / 15: tensor-core forward with 4 / 8 softmax warps per CTA (8 is the default)
   if (force_simt == 14 || force_simt == 15) { attention_tc_set_fwd_warps8(force_simt == 15); g_attn_force_simt = 0; return; }
+  // 16 / 17: 16-warp tensor-core backward with one CTA per (head, key block) / one persistent CTA per SM (the default)
+  if (force_simt == 16 || force_simt == 17) { attention_tc_set_bwd_persistent(force_simt == 17); g_attn_force_simt = 0; return; }
   if (force_simt == 9) { attention_tc_set_kv_tmem(2); g_attn_force_simt = 0; return; }   // P^T in tensor memory for dV (the default)
   g_attn_force_simt = force_simt;
 }

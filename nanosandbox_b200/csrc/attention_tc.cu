@@ -631,6 +631,8 @@ void attention_tc_set_fwd_p_tmem(int on) { g_attn_fwd_p_tmem = on; }
 void attention_tc_set_debug_buffer(long long* p) { g_attn_dbg = p; }
 static int g_attn_bwd_warps16 = 1;  // backward with 16 probability warps (attn_bwd_tc16_kernel); 0: the 8-warp kernel
 void attention_tc_set_bwd_warps16(int on) { g_attn_bwd_warps16 = on; }
+static int g_attn_bwd_persistent = 1;  // 16-warp backward as one persistent CTA per SM (attn_bwd_tc16p_kernel); 0: one CTA per item
+void attention_tc_set_bwd_persistent(int on) { g_attn_bwd_persistent = on; }
 static int g_attn_dq_direct = 0;   // 1: dQ leaves by vector reductions from registers (measured slower: 184 vs 156 us); 0: staged TMA reduce-add
 void attention_tc_set_dq_direct(int on) { g_attn_dq_direct = on; }
 // 0: every A operand from shared memory; 1: K / V as tensor-memory A operands of the S^T / dP^T MMAs (bit-identical,
@@ -1067,15 +1069,23 @@ __global__ void __launch_bounds__(448, 1)
 // four of them to overlap exp2, packed math, tensor-memory traffic and the dS^T stores, and each thread
 // works on 16 columns at a time (80 registers per thread at 704 threads).  P^T always lives in tensor memory.
 // Warps: 0 TMA, 1 MMA issue, 2..17 probabilities, 18..21 dQ write-back.
+// `release` (or null): barrier to arrive on once the values are in registers -- the caller passes it with the LAST
+// columns it reads, so that the next block's S^T / dP^T MMAs run under this half's arithmetic
 template <bool MASK>
 __device__ __forceinline__ void bwd_probs16(uint32_t taddr, const float* nlse2, const float* ndlt, float scale_log2,
-                                            int col0, int row, int qlim, bool diag, uint32_t* pk, uint32_t* dk) {
+                                            int col0, int row, int qlim, bool diag, uint32_t* pk, uint32_t* dk,
+                                            uint64_t* release) {
   using fatc::ex2;
   float sv[16], dv[16];
   ptx::tmem_ld_32x16_async(taddr + fabw::C_S, sv);
   ptx::tmem_ld_32x16_async(taddr + fabw::C_DP, dv);
   ptx::tmem_wait_ld16(sv);
   ptx::tmem_wait_ld16(dv);
+  if (release != nullptr) {
+    ptx::tc_fence_before();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(release);
+  }
   const f32x2 sc2 = pack2(scale_log2, scale_log2);
 #pragma unroll
   for (int i = 0; i < 16; i += 4) {
@@ -1258,7 +1268,7 @@ __global__ void __launch_bounds__(704, 1)
         ptx::bulk_commit();
       }
     }
-    if (et == 0) ptx::bulk_wait_all();
+    if (et == 0) ptx::bulk_wait_read<0>();          // the staging tile has been read; the adds land before the grid completes
   } else {
     // ================================ probability warps (16) ================================
     const int wg = (warp - 2) >> 2;                 // 0..3: query columns 32 wg .. 32 wg + 31 of a block
@@ -1297,13 +1307,12 @@ __global__ void __launch_bounds__(704, 1)
       for (int hf = 0; hf < 2; ++hf) {
         const uint32_t ta = tmem + lane_addr + wg * 32 + hf * 16;
         if (diag || qlim < BQ)
-          bwd_probs16<true>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8);
+          bwd_probs16<true>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8,
+                            hf == 1 ? sdp_free : nullptr);
         else
-          bwd_probs16<false>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8);
+          bwd_probs16<false>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8,
+                             hf == 1 ? sdp_free : nullptr);
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(sdp_free);
       // the P^T columns and the dS^T tile are free once the previous block's dV/dK/dQ MMAs have retired
       if (it > 0) { ptx::mbar_wait(dq_full, (it - 1) & 1); ptx::tc_fence_after(); }
       ptx::tmem_st_32x8_u32_nowait(tmem + lane_addr + C_KA + wg * 16, pk);
@@ -1337,6 +1346,309 @@ __global__ void __launch_bounds__(704, 1)
               make_uint4(pack_bf16x2(v[8 * i] * f, v[8 * i + 1] * f), pack_bf16x2(v[8 * i + 2] * f, v[8 * i + 3] * f),
                          pack_bf16x2(v[8 * i + 4] * f, v[8 * i + 5] * f), pack_bf16x2(v[8 * i + 6] * f, v[8 * i + 7] * f));
       }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem, TMEM_COLS);
+}
+
+// ---- persistent form of the 16-warp backward --------------------------------------------------------
+// One CTA per SM walks the items (key block, head) i = blockIdx.x, blockIdx.x + gridDim.x, ...; items are ordered
+// key block 0 first (the longest loops first: at T = 1024 with 144 heads on 148 SMs every CTA gets 35 or 36 query
+// blocks).  The 4 us a CTA of attn_bwd_tc16_kernel spends before its first and after its last probability block
+// (7.8 CTAs per SM: 30 of 108 us) are taken off the critical path: K / V are double-buffered and loaded during the
+// previous item, S^T / dP^T of the next item's first block are issued as soon as the last block's values have been
+// read, and dK / dV leave through the four dQ warps while the probability warps already work on the next item.
+// Roles, tensor-memory columns and the per-block protocol are those of attn_bwd_tc16_kernel; every barrier phase
+// is counted over the CTA's whole walk (g: blocks, n: items).
+__global__ void __launch_bounds__(704, 1)
+    attn_bwd_tc16p_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_dy,
+                          const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse,
+                          const float* __restrict__ delta, __nv_bfloat16* __restrict__ dqkv, int Tn, int H, int BH,
+                          int nitems, float scale, float scale_log2) {
+  using namespace fabw;
+  using fatc::sw128;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* kv_full = bars;          // [2] K, V of an item landed
+  uint64_t* kv_empty = bars + 2;     // [2] every MMA that reads them has retired
+  uint64_t* qdo_full = bars + 4;     // [QS] Q_i, dO_i landed
+  uint64_t* qdo_empty = bars + 7;    // [QS]
+  uint64_t* sdp_full = bars + 10;    // S^T, dP^T in TMEM
+  uint64_t* sdp_free = bars + 11;    // S^T / dP^T read into registers                  count 16
+  uint64_t* pds_full = bars + 12;    // P^T in TMEM, dS^T in smem                       count 16
+  uint64_t* dq_full = bars + 13;     // dV/dK/dQ MMAs of the block retired
+  uint64_t* dq_free = bars + 14;     // dQ columns read back                           count 4
+  uint64_t* dkv_full = bars + 15;    // the item's last dV/dK MMAs retired
+  uint64_t* dkv_free = bars + 16;    // dK / dV read back                               count 4
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  float* stat = reinterpret_cast<float*>(smem + OFF_STAT);
+  static_assert(QS == 3, "barrier layout");
+  static_assert(OFF_PT + 2 * TILE <= OFF_DS, "second K / V buffer");
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int C = H * HD;
+  const int nq = (Tn + BQ - 1) / BQ;
+  const int stride = static_cast<int>(gridDim.x);
+
+  if (threadIdx.x == 0) {
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+    ptx::prefetch_tmap(&tmap_qkv);
+    ptx::prefetch_tmap(&tmap_dy);
+    ptx::prefetch_tmap(&tmap_dq);
+  }
+  if (warp == 0 && lane < 17) {
+    const uint32_t count = (lane == 11 || lane == 12) ? 16u : ((lane == 14 || lane == 16) ? 4u : 1u);
+    ptx::mbar_init(&bars[lane], count);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  pdl_wait();
+  pdl_trigger();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0, n = 0;                             // Q / dO ring slot; items so far
+      uint32_t sph = 0;                             // parity of the slot's use count
+      for (int item = blockIdx.x; item < nitems; item += stride, ++n) {
+        const int jb = item / BH, bh = item - jb * BH, b = bh / H, h = bh - b * H;
+        const int row_base = b * Tn, kb = n & 1;
+        uint8_t* kv = smem + (kb ? OFF_PT : OFF_K);
+        ptx::mbar_wait(&kv_empty[kb], ((n >> 1) & 1) ^ 1);
+        ptx::mbar_expect_tx(&kv_full[kb], 2 * TILE);
+        ptx::tma_load_2d(kv, &tmap_qkv, &kv_full[kb], C + h * HD, row_base + jb * BKV);
+        ptx::tma_load_2d(kv + TILE, &tmap_qkv, &kv_full[kb], 2 * C + h * HD, row_base + jb * BKV);
+        for (int qb = jb; qb < nq; ++qb) {
+          ptx::mbar_wait(&qdo_empty[s], sph ^ 1u);
+          ptx::mbar_expect_tx(&qdo_full[s], 2 * TILE);
+          ptx::tma_load_2d(smem + OFF_Q + s * TILE, &tmap_qkv, &qdo_full[s], h * HD, row_base + qb * BQ);
+          ptx::tma_load_2d(smem + OFF_DO + s * TILE, &tmap_dy, &qdo_full[s], h * HD, row_base + qb * BQ);
+          if (++s == QS) { s = 0; sph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t ID_SDP = ptx::umma_idesc_bf16(128, 128, false, false);  // S^T, dP^T
+    constexpr uint32_t ID_DKV = ptx::umma_idesc_bf16(128, 64, false, true);    // dV, dK: B MN-major
+    constexpr uint32_t ID_DQ = ptx::umma_idesc_bf16(128, 64, true, true);      // dQ: A and B MN-major
+    const uint32_t sb = ptx::smem_u32(smem);
+    const uint64_t dDS = ptx::umma_smem_desc_sw128(sb + OFF_DS, 16, 1024);
+    const uint64_t dDSmn = ptx::umma_smem_desc_sw128(sb + OFF_DS, TILE, 1024);
+    auto issue_sdp = [&](int s, int kb) {
+      const uint32_t kvb = sb + (kb ? OFF_PT : OFF_K);
+      const uint64_t dK_ = ptx::umma_smem_desc_sw128(kvb, 16, 1024);
+      const uint64_t dV_ = ptx::umma_smem_desc_sw128(kvb + TILE, 16, 1024);
+      const uint64_t q_k = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, 16, 1024);
+      const uint64_t do_k = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, 16, 1024);
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tmem + C_S, dK_ + static_cast<uint64_t>(2 * k), q_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tmem + C_DP, dV_ + static_cast<uint64_t>(2 * k), do_k + static_cast<uint64_t>(2 * k), ID_SDP, k > 0);
+        ptx::umma_commit(sdp_full);
+      }
+      __syncwarp();
+    };
+    int item = blockIdx.x;
+    if (item < nitems) {
+      int nit = nq - item / BH, it = 0, n = 0, s = 0;
+      uint32_t sph = 0, g = 0;
+      ptx::mbar_wait(&kv_full[0], 0);
+      ptx::mbar_wait(&qdo_full[0], 0);
+      ptx::tc_fence_after();
+      issue_sdp(0, 0);
+      while (true) {
+        // the block after this one: the next query block of the item, or the first of the CTA's next item
+        int n_item = item, n_it = it + 1, n_nit = nit, n_n = n;
+        if (n_it == nit) {
+          n_item = item + stride; n_it = 0; n_n = n + 1;
+          if (n_item < nitems) n_nit = nq - n_item / BH;
+        }
+        const bool has_next = n_item < nitems;
+        int ns = s + 1;
+        uint32_t nsph = sph;
+        if (ns == QS) { ns = 0; nsph ^= 1u; }
+        if (has_next) {
+          ptx::mbar_wait(sdp_free, g & 1u);
+          ptx::mbar_wait(&qdo_full[ns], nsph);
+          if (n_it == 0) ptx::mbar_wait(&kv_full[n_n & 1], (n_n >> 1) & 1);
+          ptx::tc_fence_after();
+          issue_sdp(ns, n_n & 1);
+        }
+        ptx::mbar_wait(pds_full, g & 1u);
+        if (it == 0 && n > 0) ptx::mbar_wait(dkv_free, (n - 1) & 1);   // the previous item's dK / dV have been read
+        ptx::tc_fence_after();
+        const uint64_t q_mn = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, TILE, 1024);
+        const uint64_t do_mn = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, TILE, 1024);
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)      // dV += P^T dO, A = P^T from tensor memory (8 packed columns per 16 queries)
+            ptx::umma_bf16_ts(tmem + C_DV, tmem + C_KA + 8 * k, do_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint64_t a_off = static_cast<uint64_t>(((k / 4) * TILE + (k % 4) * 32) >> 4);
+            ptx::umma_bf16(tmem + C_DK, dDS + a_off, q_mn + static_cast<uint64_t>(128 * k), ID_DKV, (it > 0 || k > 0) ? 1u : 0u);
+          }
+        }
+        __syncwarp();
+        if (g > 0) { ptx::mbar_wait(dq_free, (g - 1) & 1u); ptx::tc_fence_after(); }
+        const uint64_t dKmn = ptx::umma_smem_desc_sw128(sb + ((n & 1) ? OFF_PT : OFF_K), TILE, 1024);
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            ptx::umma_bf16(tmem + C_DQ, dDSmn + static_cast<uint64_t>(128 * k), dKmn + static_cast<uint64_t>(128 * k), ID_DQ, k > 0);
+          ptx::umma_commit(dq_full);
+          ptx::umma_commit(&qdo_empty[s]);
+          if (it == nit - 1) {
+            ptx::umma_commit(dkv_full);
+            ptx::umma_commit(&kv_empty[n & 1]);
+          }
+        }
+        __syncwarp();
+        if (!has_next) break;
+        item = n_item; it = n_it; nit = n_nit; n = n_n; s = ns; sph = nsph; ++g;
+      }
+    }
+  } else if (warp >= 18) {
+    // ---- dQ write-back warps: TMEM (lane = query row) -> x scale -> swizzled smem -> TMA reduce-add; after an
+    // item's last block the same warps take dK / dV (lane = key row) out of tensor memory ----
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;
+    const int et = threadIdx.x - 576;               // 0..127
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    uint32_t g = 0;
+    int n = 0;
+    for (int item = blockIdx.x; item < nitems; item += stride, ++n) {
+      const int jb = item / BH, bh = item - jb * BH, b = bh / H, h = bh - b * H;
+      const int row_base = b * Tn;
+      for (int qb = jb; qb < nq; ++qb, ++g) {
+        ptx::mbar_wait(dq_full, g & 1u);
+        ptx::tc_fence_after();
+        float v[32];
+        ptx::tmem_ld_32x32(tmem + lane_addr + C_DQ, v);
+        if (et == 0) ptx::bulk_wait_read<0>();        // both staging atoms drained
+        ptx::named_bar_sync(1, 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<float4*>(smem + OFF_DQ + sw128(row, i)) =
+              make_float4(v[4 * i] * scale, v[4 * i + 1] * scale, v[4 * i + 2] * scale, v[4 * i + 3] * scale);
+        ptx::tmem_ld_32x32(tmem + lane_addr + C_DQ + 32, v);
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(dq_free);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<float4*>(smem + OFF_DQ + TILE + sw128(row, i)) =
+              make_float4(v[4 * i] * scale, v[4 * i + 1] * scale, v[4 * i + 2] * scale, v[4 * i + 3] * scale);
+        ptx::fence_proxy_async();
+        ptx::named_bar_sync(1, 128);
+        if (et == 0) {
+          ptx::tma_reduce_add_2d(&tmap_dq, smem + OFF_DQ, h * HD, row_base + qb * BQ);
+          ptx::tma_reduce_add_2d(&tmap_dq, smem + OFF_DQ + TILE, h * HD + 32, row_base + qb * BQ);
+          ptx::bulk_commit();
+        }
+      }
+      // dK (x scale) and dV of the item's key block, 32 columns at a time
+      ptx::mbar_wait(dkv_full, n & 1);
+      ptx::tc_fence_after();
+      const int key = jb * BKV + row;
+      const bool live = key < Tn;
+      __nv_bfloat16* out = dqkv + (static_cast<size_t>(row_base) + (live ? key : 0)) * (3 * C) + C + h * HD;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {                  // dK columns 0-31, 32-63, then dV
+        float v[32];
+        ptx::tmem_ld_32x32(tmem + lane_addr + (c < 2 ? C_DK : C_DV) + (c & 1) * 32, v);
+        if (c == 3) {                                // the accumulators may be overwritten by the next item
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(dkv_free);
+        }
+        const float f = c < 2 ? scale : 1.f;
+        if (live) {
+          uint4* o = reinterpret_cast<uint4*>(out + (c >> 1) * C + (c & 1) * 32);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            o[i] = make_uint4(pack_bf16x2(v[8 * i] * f, v[8 * i + 1] * f), pack_bf16x2(v[8 * i + 2] * f, v[8 * i + 3] * f),
+                              pack_bf16x2(v[8 * i + 4] * f, v[8 * i + 5] * f), pack_bf16x2(v[8 * i + 6] * f, v[8 * i + 7] * f));
+        }
+      }
+    }
+    if (et == 0) ptx::bulk_wait_read<0>();          // the staging tile has been read; the adds land before the grid completes
+  } else {
+    // ================================ probability warps (16) ================================
+    const int wg = (warp - 2) >> 2;                 // 0..3: query columns 32 wg .. 32 wg + 31 of a block
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;                 // TMEM lane: key row
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    // per-query statistics as in attn_bwd_tc16_kernel: fetched one block ahead (across items too), looked at
+    // only when they are stored at the top of the block they belong to
+    const int gt = (threadIdx.x - 64) & 127;        // 0..127 within the group
+    const bool loader = gt < 64, is_lse = gt < 32;
+    const int scol = wg * 32 + (gt & 31);            // the query column (within the block) this thread fetches
+    auto load_stat = [&](const float* stats, int qb) -> float {
+      const int qg = qb * BQ + scol;
+      if (!loader || qg >= Tn) return 0.f;
+      return stats[qg];
+    };
+    auto stat_row = [&](int item) -> const float* {   // this thread's statistic (lse or delta) of the item's head
+      const int bh = item % BH;
+      return (is_lse ? lse : delta) + static_cast<size_t>(bh) * Tn;
+    };
+    int item = blockIdx.x;
+    uint32_t g = 0;
+    const float* srow = item < nitems ? stat_row(item) : lse;
+    float st_next = item < nitems ? load_stat(srow, item / BH) : 0.f;
+    for (; item < nitems; item += stride) {
+      const int jb = item / BH;
+      const int n_item = item + stride;
+      const float* srow_n = n_item < nitems ? stat_row(n_item) : srow;
+      const int jb_n = n_item < nitems ? n_item / BH : 0;
+      for (int qb = jb; qb < nq; ++qb, ++g) {
+        const uint32_t gp = g & 1u;
+        if (loader) stat[gp * 256 + (is_lse ? 0 : 128) + scol] = is_lse ? -st_next * 1.4426950408889634f : -st_next;
+        if (qb + 1 < nq) st_next = load_stat(srow, qb + 1);
+        else if (n_item < nitems) st_next = load_stat(srow_n, jb_n);
+        ptx::named_bar_sync(4 + wg, 128);
+        const float* nlse2 = stat + gp * 256 + wg * 32;
+        const float* ndlt = nlse2 + 128;
+        const bool diag = (qb == jb);
+        const int qlim = Tn - qb * BQ;                // query columns >= qlim are padding
+        ptx::mbar_wait(sdp_full, gp);
+        ptx::tc_fence_after();
+        uint32_t pk[16], dk[16];                      // packed bf16 pairs of P^T and dS^T (32 columns)
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          const uint32_t ta = tmem + lane_addr + wg * 32 + hf * 16;
+          if (diag || qlim < BQ)
+            bwd_probs16<true>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8,
+                              hf == 1 ? sdp_free : nullptr);
+          else
+            bwd_probs16<false>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8,
+                               hf == 1 ? sdp_free : nullptr);
+        }
+        // the P^T columns and the dS^T tile are free once the previous block's dV/dK/dQ MMAs have retired
+        if (g > 0) { ptx::mbar_wait(dq_full, (g - 1) & 1u); ptx::tc_fence_after(); }
+        ptx::tmem_st_32x8_u32_nowait(tmem + lane_addr + C_KA + wg * 16, pk);
+        ptx::tmem_st_32x8_u32_nowait(tmem + lane_addr + C_KA + wg * 16 + 8, pk + 8);
+        uint8_t* dst = smem + OFF_DS + (wg >> 1) * TILE;
+        const int q0 = (wg & 1) * 4;                  // first 16-byte chunk of this group's 32 columns in the 128-byte row
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          *reinterpret_cast<uint4*>(dst + sw128(row, q0 + i)) = make_uint4(dk[4 * i], dk[4 * i + 1], dk[4 * i + 2], dk[4 * i + 3]);
+        ptx::tmem_wait_st();
+        ptx::tc_fence_before();
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(pds_full);
+      }
+      srow = srow_n;
     }
   }
   ptx::tc_fence_before();
@@ -1419,8 +1731,20 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
       cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
       NSB_REQUIRE(e == cudaSuccess, "attention_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     }
-    launch_pdl(attn_bwd_tc16_kernel, dim3(grid), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta,
-               static_cast<__nv_bfloat16*>(dqkv), T, H, scale, scale * 1.4426950408889634f);
+    if (g_attn_bwd_persistent) {
+      static PerDeviceOnce attr16p;
+      if (attr16p.first_use()) {
+        cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc16p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        NSB_REQUIRE(e == cudaSuccess, "attention_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      }
+      const int nitems = static_cast<int>(grid.x * grid.y);
+      const int ctas = nitems < sm_count() ? nitems : sm_count();
+      launch_pdl(attn_bwd_tc16p_kernel, dim3(ctas), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta,
+                 static_cast<__nv_bfloat16*>(dqkv), T, H, B * H, nitems, scale, scale * 1.4426950408889634f);
+    } else {
+      launch_pdl(attn_bwd_tc16_kernel, dim3(grid), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta,
+                 static_cast<__nv_bfloat16*>(dqkv), T, H, scale, scale * 1.4426950408889634f);
+    }
   } else {
     launch_pdl(attn_bwd_tc_kernel, dim3(grid), dim3(448), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
                scale, scale * 1.4426950408889634f, dq_acc, g_attn_dq_direct, g_attn_kv_tmem, g_attn_dbg);

@@ -481,13 +481,13 @@ def test_attention_bf16_paths(path, B, T, H):
         lib.nsb_attention_debug_config(0)
 
 
-@pytest.mark.parametrize("mode", [12, 14, 5, 6, 10])
+@pytest.mark.parametrize("mode", [12, 14, 5, 6, 10, 16])
 @pytest.mark.parametrize("B,T,H", [(2, 256, 3), (1, 1000, 2)])
 def test_attention_tc_kernel_variants(mode, B, T, H):
     """The earlier forms of the tcgen05 kernels stay selectable for A/B runs (8 probability warps backward: 12,
     4 softmax warps forward: 14, every A operand from shared memory: 5, K/V from tensor memory: 6, forward P
-    through shared memory: 10; the 4-warp forward is the one modes 10 / 11 act on): each must pass the same
-    parity check as the defaults."""
+    through shared memory: 10; the 4-warp forward is the one modes 10 / 11 act on; 16-warp backward with one CTA
+    per (head, key block) instead of the persistent walk: 16): each must pass the same parity check as the defaults."""
     lib = _lib.load()
     if mode in (5, 6):
         lib.nsb_attention_debug_config(12)      # these two switches act on the 8-warp backward kernel
@@ -497,7 +497,7 @@ def test_attention_tc_kernel_variants(mode, B, T, H):
     try:
         test_attention_fwd_bwd(torch.bfloat16, B, T, H, 64)
     finally:
-        for m in (13, 15, 9, 11):               # back to the defaults
+        for m in (13, 15, 9, 11, 17):           # back to the defaults
             lib.nsb_attention_debug_config(m)
 
 
