@@ -24,6 +24,8 @@ namespace nsb {
 
 int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint64_t d1, uint64_t row_stride,
                  uint32_t b0, uint32_t b1);
+int make_tmap_3d_bf16(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t row_stride,
+                      uint64_t slice_stride, uint32_t b0, uint32_t b1);
 
 namespace fatc {
 constexpr int BQ = 128, BKV = 128, HD = 64;
@@ -1075,6 +1077,11 @@ template <bool MASK>
 __device__ __forceinline__ void bwd_probs16(uint32_t taddr, const float* nlse2, const float* ndlt, float scale_log2,
                                             int col0, int row, int qlim, bool diag, uint32_t* pk, uint32_t* dk,
                                             uint64_t* release) {
+  // MASK: query column c of this key row survives iff lo <= c < qlim, lo = row on the diagonal block, else 0:
+  // one unsigned compare and a select per element (written with && / || the compiler branches per element,
+  // and on the diagonal every one of those branches diverges)
+  const int lo = diag ? row : 0;
+  const uint32_t span = qlim > lo ? static_cast<uint32_t>(qlim - lo) : 0u;
   using fatc::ex2;
   float sv[16], dv[16];
   ptx::tmem_ld_32x16_async(taddr + fabw::C_S, sv);
@@ -1099,8 +1106,8 @@ __device__ __forceinline__ void bwd_probs16(uint32_t taddr, const float* nlse2, 
       float p0 = ex2(a0), p1 = ex2(a1);
       if (MASK) {
         const int col = col0 + i + e;                          // query column within the block
-        p0 = ((col < qlim) && (!diag || col >= row)) ? p0 : 0.f;
-        p1 = ((col + 1 < qlim) && (!diag || col + 1 >= row)) ? p1 : 0.f;
+        p0 = (static_cast<uint32_t>(col - lo) < span) ? p0 : 0.f;
+        p1 = (static_cast<uint32_t>(col + 1 - lo) < span) ? p1 : 0.f;
       }
       float d0, d1;
       unpack2(mul2(pack2(p0, p1), add2(pack2(dv[i + e], dv[i + e + 1]), pack2(nd[e], nd[e + 1]))), d0, d1);
@@ -1362,11 +1369,14 @@ __global__ void __launch_bounds__(704, 1)
 // read, and dK / dV leave through the four dQ warps while the probability warps already work on the next item.
 // Roles, tensor-memory columns and the per-block protocol are those of attn_bwd_tc16_kernel; every barrier phase
 // is counted over the CTA's whole walk (g: blocks, n: items).
+// TRACE: clock64 stamps of CTA 0 into dbg (tools/attn_bwd_timing.py --persistent): one probability warp at
+// dbg[8 g + k], the MMA warp at dbg[512 + 8 g + k], one dQ warp at dbg[1024 + 4 g + k], g = block number < 48
+template <bool TRACE>
 __global__ void __launch_bounds__(704, 1)
     attn_bwd_tc16p_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_dy,
-                          const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse,
-                          const float* __restrict__ delta, __nv_bfloat16* __restrict__ dqkv, int Tn, int H, int BH,
-                          int nitems, float scale, float scale_log2) {
+                          const __grid_constant__ CUtensorMap tmap_dq, const __grid_constant__ CUtensorMap tmap_dkv,
+                          const float* __restrict__ lse, const float* __restrict__ delta, int Tn, int H, int BH,
+                          int nitems, float scale, float scale_log2, long long* __restrict__ dbg) {
   using namespace fabw;
   using fatc::sw128;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -1380,8 +1390,8 @@ __global__ void __launch_bounds__(704, 1)
   uint64_t* pds_full = bars + 12;    // P^T in TMEM, dS^T in smem                       count 16
   uint64_t* dq_full = bars + 13;     // dV/dK/dQ MMAs of the block retired
   uint64_t* dq_free = bars + 14;     // dQ columns read back                           count 4
-  uint64_t* dkv_full = bars + 15;    // the item's last dV/dK MMAs retired
   uint64_t* dkv_free = bars + 16;    // dK / dV read back                               count 4
+  uint64_t* stat_full = bars + 17;   // [2] per-query statistics of a block in shared memory   count 4
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
   float* stat = reinterpret_cast<float*>(smem + OFF_STAT);
   static_assert(QS == 3, "barrier layout");
@@ -1391,15 +1401,19 @@ __global__ void __launch_bounds__(704, 1)
   const int C = H * HD;
   const int nq = (Tn + BQ - 1) / BQ;
   const int stride = static_cast<int>(gridDim.x);
+  auto stamp = [&](int base, uint32_t g, int k) {
+    if (TRACE && blockIdx.x == 0 && lane == 0 && g < 48) dbg[base + (base == 1024 ? 4 : 8) * g + k] = clock64();
+  };
 
   if (threadIdx.x == 0) {
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
     ptx::prefetch_tmap(&tmap_qkv);
     ptx::prefetch_tmap(&tmap_dy);
     ptx::prefetch_tmap(&tmap_dq);
+    ptx::prefetch_tmap(&tmap_dkv);
   }
-  if (warp == 0 && lane < 17) {
-    const uint32_t count = (lane == 11 || lane == 12) ? 16u : ((lane == 14 || lane == 16) ? 4u : 1u);
+  if (warp == 0 && lane < 19) {
+    const uint32_t count = (lane == 11 || lane == 12) ? 16u : ((lane == 14 || lane >= 16) ? 4u : 1u);
     ptx::mbar_init(&bars[lane], count);
     ptx::fence_mbar_init();
   }
@@ -1475,16 +1489,22 @@ __global__ void __launch_bounds__(704, 1)
         int ns = s + 1;
         uint32_t nsph = sph;
         if (ns == QS) { ns = 0; nsph ^= 1u; }
+        stamp(512, g, 0);
         if (has_next) {
           ptx::mbar_wait(sdp_free, g & 1u);
+          stamp(512, g, 1);
           ptx::mbar_wait(&qdo_full[ns], nsph);
           if (n_it == 0) ptx::mbar_wait(&kv_full[n_n & 1], (n_n >> 1) & 1);
           ptx::tc_fence_after();
+          stamp(512, g, 2);
           issue_sdp(ns, n_n & 1);
         }
+        stamp(512, g, 3);
         ptx::mbar_wait(pds_full, g & 1u);
+        stamp(512, g, 4);
         if (it == 0 && n > 0) ptx::mbar_wait(dkv_free, (n - 1) & 1);   // the previous item's dK / dV have been read
         ptx::tc_fence_after();
+        stamp(512, g, 5);
         const uint64_t q_mn = ptx::umma_smem_desc_sw128(sb + OFF_Q + s * TILE, TILE, 1024);
         const uint64_t do_mn = ptx::umma_smem_desc_sw128(sb + OFF_DO + s * TILE, TILE, 1024);
         if (ptx::elect_one()) {
@@ -1498,7 +1518,9 @@ __global__ void __launch_bounds__(704, 1)
           }
         }
         __syncwarp();
+        stamp(512, g, 6);
         if (g > 0) { ptx::mbar_wait(dq_free, (g - 1) & 1u); ptx::tc_fence_after(); }
+        stamp(512, g, 7);
         const uint64_t dKmn = ptx::umma_smem_desc_sw128(sb + ((n & 1) ? OFF_PT : OFF_K), TILE, 1024);
         if (ptx::elect_one()) {
 #pragma unroll
@@ -1506,10 +1528,7 @@ __global__ void __launch_bounds__(704, 1)
             ptx::umma_bf16(tmem + C_DQ, dDSmn + static_cast<uint64_t>(128 * k), dKmn + static_cast<uint64_t>(128 * k), ID_DQ, k > 0);
           ptx::umma_commit(dq_full);
           ptx::umma_commit(&qdo_empty[s]);
-          if (it == nit - 1) {
-            ptx::umma_commit(dkv_full);
-            ptx::umma_commit(&kv_empty[n & 1]);
-          }
+          if (it == nit - 1) ptx::umma_commit(&kv_empty[n & 1]);
         }
         __syncwarp();
         if (!has_next) break;
@@ -1523,14 +1542,80 @@ __global__ void __launch_bounds__(704, 1)
     const int row = qd * 32 + lane;
     const int et = threadIdx.x - 576;               // 0..127
     const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    // These warps also feed the probability warps their per-query statistics: thread et fetches lse and delta of
+    // query et of the block TWO ahead in the CTA's walk (across items) and stores them negated, lse in log2
+    // units (see bwd_probs16), into the buffer that block's parity names.  That buffer was last read for block
+    // g, whose arithmetic is over once dq_full(g) has completed.
+    int la_item = blockIdx.x, la_qb = la_item < nitems ? la_item / BH : 0;
+    auto la_load = [&](float& l, float& d) {
+      l = 0.f; d = 0.f;
+      const int q = la_qb * BQ + et;
+      if (la_item < nitems && q < Tn) {
+        const size_t o = static_cast<size_t>(la_item % BH) * Tn + q;
+        l = lse[o]; d = delta[o];
+      }
+    };
+    auto la_store = [&](uint32_t blk, float l, float d) {
+      stat[(blk & 1u) * 256 + et] = -l * 1.4426950408889634f;
+      stat[(blk & 1u) * 256 + 128 + et] = -d;
+      if (++la_qb == nq) {                           // on to the next block of the walk
+        la_item += stride;
+        if (la_item < nitems) la_qb = la_item / BH;
+      }
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&stat_full[blk & 1u]);
+    };
+    {
+      float l, d;
+      la_load(l, d); la_store(0, l, d);
+      la_load(l, d); la_store(1, l, d);
+    }
     uint32_t g = 0;
     int n = 0;
     for (int item = blockIdx.x; item < nitems; item += stride, ++n) {
       const int jb = item / BH, bh = item - jb * BH, b = bh / H, h = bh - b * H;
       const int row_base = b * Tn;
       for (int qb = jb; qb < nq; ++qb, ++g) {
+        if (warp == 18) stamp(1024, g, 0);
+        float st_l, st_d;
+        la_load(st_l, st_d);                         // in flight under the wait
         ptx::mbar_wait(dq_full, g & 1u);
         ptx::tc_fence_after();
+        if (warp == 18) stamp(1024, g, 1);
+        if (qb == nq - 1) {
+          // The item's last block: its commit also covers the last dV / dK MMAs.  dK (x scale) and dV go first --
+          // the next item's first dV / dK MMAs wait for these accumulators (dkv_free), nothing waits for this
+          // block's dQ: tensor memory (lane = key row) -> bf16 -> the two staging tiles (128-byte rows,
+          // swizzled) -> one TMA store each, clipped at the end of the sequence.  (Written from registers, 64
+          // bytes per thread at a row stride of 3 C, these stores held the SM's load/store unit for several
+          // thousand clocks, and the probability warps' shared-memory traffic with it.)
+          if (et == 0) ptx::bulk_wait_read<0>();        // the previous dQ tile has left the staging buffers
+          ptx::named_bar_sync(1, 128);
+#pragma unroll 1
+          for (int c = 0; c < 4; ++c) {                // dK columns 0-31, 32-63, then dV
+            float v[32];
+            ptx::tmem_ld_32x32(tmem + lane_addr + (c < 2 ? C_DK : C_DV) + (c & 1) * 32, v);
+            if (c == 3) {                              // the accumulators may be overwritten by the next item
+              ptx::tc_fence_before();
+              __syncwarp();
+              if (lane == 0) ptx::mbar_arrive(dkv_free);
+            }
+            const float f = c < 2 ? scale : 1.f;
+            uint8_t* dst = smem + OFF_DQ + (c >> 1) * TILE;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(dst + sw128(row, (c & 1) * 4 + i)) =
+                  make_uint4(pack_bf16x2(v[8 * i] * f, v[8 * i + 1] * f), pack_bf16x2(v[8 * i + 2] * f, v[8 * i + 3] * f),
+                             pack_bf16x2(v[8 * i + 4] * f, v[8 * i + 5] * f), pack_bf16x2(v[8 * i + 6] * f, v[8 * i + 7] * f));
+          }
+          ptx::fence_proxy_async();
+          ptx::named_bar_sync(1, 128);
+          if (et == 0) {
+            ptx::tma_store_3d(&tmap_dkv, smem + OFF_DQ, C + h * HD, jb * BKV, b);
+            ptx::tma_store_3d(&tmap_dkv, smem + OFF_DQ + TILE, 2 * C + h * HD, jb * BKV, b);
+            ptx::bulk_commit();
+          }
+        }
         float v[32];
         ptx::tmem_ld_32x32(tmem + lane_addr + C_DQ, v);
         if (et == 0) ptx::bulk_wait_read<0>();        // both staging atoms drained
@@ -1543,6 +1628,8 @@ __global__ void __launch_bounds__(704, 1)
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(dq_free);
+        la_store(g + 2, st_l, st_d);                 // after the release of the dQ columns, which the MMA warp waits for
+        if (warp == 18) stamp(1024, g, 2);
 #pragma unroll
         for (int i = 0; i < 8; ++i)
           *reinterpret_cast<float4*>(smem + OFF_DQ + TILE + sw128(row, i)) =
@@ -1554,30 +1641,7 @@ __global__ void __launch_bounds__(704, 1)
           ptx::tma_reduce_add_2d(&tmap_dq, smem + OFF_DQ + TILE, h * HD + 32, row_base + qb * BQ);
           ptx::bulk_commit();
         }
-      }
-      // dK (x scale) and dV of the item's key block, 32 columns at a time
-      ptx::mbar_wait(dkv_full, n & 1);
-      ptx::tc_fence_after();
-      const int key = jb * BKV + row;
-      const bool live = key < Tn;
-      __nv_bfloat16* out = dqkv + (static_cast<size_t>(row_base) + (live ? key : 0)) * (3 * C) + C + h * HD;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {                  // dK columns 0-31, 32-63, then dV
-        float v[32];
-        ptx::tmem_ld_32x32(tmem + lane_addr + (c < 2 ? C_DK : C_DV) + (c & 1) * 32, v);
-        if (c == 3) {                                // the accumulators may be overwritten by the next item
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(dkv_free);
-        }
-        const float f = c < 2 ? scale : 1.f;
-        if (live) {
-          uint4* o = reinterpret_cast<uint4*>(out + (c >> 1) * C + (c & 1) * 32);
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            o[i] = make_uint4(pack_bf16x2(v[8 * i] * f, v[8 * i + 1] * f), pack_bf16x2(v[8 * i + 2] * f, v[8 * i + 3] * f),
-                              pack_bf16x2(v[8 * i + 4] * f, v[8 * i + 5] * f), pack_bf16x2(v[8 * i + 6] * f, v[8 * i + 7] * f));
-        }
+        if (warp == 18) stamp(1024, g, 3);
       }
     }
     if (et == 0) ptx::bulk_wait_read<0>();          // the staging tile has been read; the adds land before the grid completes
@@ -1587,54 +1651,41 @@ __global__ void __launch_bounds__(704, 1)
     const int qd = warp & 3;
     const int row = qd * 32 + lane;                 // TMEM lane: key row
     const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
-    // per-query statistics as in attn_bwd_tc16_kernel: fetched one block ahead (across items too), looked at
-    // only when they are stored at the top of the block they belong to
-    const int gt = (threadIdx.x - 64) & 127;        // 0..127 within the group
-    const bool loader = gt < 64, is_lse = gt < 32;
-    const int scol = wg * 32 + (gt & 31);            // the query column (within the block) this thread fetches
-    auto load_stat = [&](const float* stats, int qb) -> float {
-      const int qg = qb * BQ + scol;
-      if (!loader || qg >= Tn) return 0.f;
-      return stats[qg];
-    };
-    auto stat_row = [&](int item) -> const float* {   // this thread's statistic (lse or delta) of the item's head
-      const int bh = item % BH;
-      return (is_lse ? lse : delta) + static_cast<size_t>(bh) * Tn;
-    };
-    int item = blockIdx.x;
+    // the per-query statistics of a block are put into shared memory by the dQ warps (stat_full)
+    const int tbase = warp == 2 ? 0 : (warp == 4 ? 1536 : -1);   // traced warps: 2 (above the diagonal), 4 (on it)
     uint32_t g = 0;
-    const float* srow = item < nitems ? stat_row(item) : lse;
-    float st_next = item < nitems ? load_stat(srow, item / BH) : 0.f;
-    for (; item < nitems; item += stride) {
+    for (int item = blockIdx.x; item < nitems; item += stride) {
       const int jb = item / BH;
-      const int n_item = item + stride;
-      const float* srow_n = n_item < nitems ? stat_row(n_item) : srow;
-      const int jb_n = n_item < nitems ? n_item / BH : 0;
       for (int qb = jb; qb < nq; ++qb, ++g) {
         const uint32_t gp = g & 1u;
-        if (loader) stat[gp * 256 + (is_lse ? 0 : 128) + scol] = is_lse ? -st_next * 1.4426950408889634f : -st_next;
-        if (qb + 1 < nq) st_next = load_stat(srow, qb + 1);
-        else if (n_item < nitems) st_next = load_stat(srow_n, jb_n);
-        ptx::named_bar_sync(4 + wg, 128);
+        if (tbase >= 0) stamp(tbase, g, 0);
+        ptx::mbar_wait(&stat_full[gp], (g >> 1) & 1u);
         const float* nlse2 = stat + gp * 256 + wg * 32;
         const float* ndlt = nlse2 + 128;
         const bool diag = (qb == jb);
         const int qlim = Tn - qb * BQ;                // query columns >= qlim are padding
+        if (tbase >= 0) stamp(tbase, g, 1);
         ptx::mbar_wait(sdp_full, gp);
         ptx::tc_fence_after();
+        if (tbase >= 0) stamp(tbase, g, 2);
         uint32_t pk[16], dk[16];                      // packed bf16 pairs of P^T and dS^T (32 columns)
+        // (Skipping the warps whose 32 x 32 piece of a diagonal block is entirely masked, and taking the unmasked
+        // form for those entirely below the diagonal, was measured slower: 103.7 against 102.6 us.)
+        const int tri = (diag || qlim < BQ) ? 1 : 2;
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
           const uint32_t ta = tmem + lane_addr + wg * 32 + hf * 16;
-          if (diag || qlim < BQ)
+          if (tri == 1)
             bwd_probs16<true>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8,
                               hf == 1 ? sdp_free : nullptr);
-          else
+          else if (tri == 2)
             bwd_probs16<false>(ta, nlse2 + hf * 16, ndlt + hf * 16, scale_log2, wg * 32 + hf * 16, row, qlim, diag, pk + hf * 8, dk + hf * 8,
                                hf == 1 ? sdp_free : nullptr);
+          if (TRACE && tbase >= 0 && blockIdx.x == 0 && lane == 0 && g < 48) dbg[tbase + 8 * g + 3 + hf] = clock64() + (pk[hf * 8] & 0) + (dk[hf * 8 + 7] & 0);
         }
         // the P^T columns and the dS^T tile are free once the previous block's dV/dK/dQ MMAs have retired
         if (g > 0) { ptx::mbar_wait(dq_full, (g - 1) & 1u); ptx::tc_fence_after(); }
+        if (tbase >= 0) stamp(tbase, g, 5);
         ptx::tmem_st_32x8_u32_nowait(tmem + lane_addr + C_KA + wg * 16, pk);
         ptx::tmem_st_32x8_u32_nowait(tmem + lane_addr + C_KA + wg * 16 + 8, pk + 8);
         uint8_t* dst = smem + OFF_DS + (wg >> 1) * TILE;
@@ -1647,8 +1698,8 @@ __global__ void __launch_bounds__(704, 1)
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(pds_full);
+        if (tbase >= 0) stamp(tbase, g, 6);
       }
-      srow = srow_n;
     }
   }
   ptx::tc_fence_before();
@@ -1725,7 +1776,7 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
       static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), delta, B, T, H);
   const dim3 grid(B * H, (T + BKV - 1) / BKV);
   const float scale = 1.0f / sqrtf(static_cast<float>(HD));
-  if (g_attn_bwd_warps16 && g_attn_dbg == nullptr) {
+  if (g_attn_bwd_warps16 && (g_attn_dbg == nullptr || g_attn_bwd_persistent)) {
     static PerDeviceOnce attr16;
     if (attr16.first_use()) {
       cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
@@ -1734,13 +1785,23 @@ int attention_bwd_tc_launch(const void* qkv, const void* y, const void* dy, cons
     if (g_attn_bwd_persistent) {
       static PerDeviceOnce attr16p;
       if (attr16p.first_use()) {
-        cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc16p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc16p_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(attn_bwd_tc16p_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         NSB_REQUIRE(e == cudaSuccess, "attention_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       }
       const int nitems = static_cast<int>(grid.x * grid.y);
       const int ctas = nitems < sm_count() ? nitems : sm_count();
-      launch_pdl(attn_bwd_tc16p_kernel, dim3(ctas), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta,
-                 static_cast<__nv_bfloat16*>(dqkv), T, H, B * H, nitems, scale, scale * 1.4426950408889634f);
+      CUtensorMap tdkv;
+      rc = make_tmap_3d_bf16(&tdkv, dqkv, static_cast<uint64_t>(3) * C, T, B, static_cast<uint64_t>(3) * C,
+                             static_cast<uint64_t>(T) * 3 * C, HD, BKV);
+      if (rc) return rc;
+      if (g_attn_dbg != nullptr)
+        launch_pdl(attn_bwd_tc16p_kernel<true>, dim3(ctas), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, tdkv, lse, delta,
+                   T, H, B * H, nitems, scale, scale * 1.4426950408889634f, g_attn_dbg);
+      else
+        launch_pdl(attn_bwd_tc16p_kernel<false>, dim3(ctas), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, tdkv, lse, delta,
+                   T, H, B * H, nitems, scale, scale * 1.4426950408889634f, static_cast<long long*>(nullptr));
     } else {
       launch_pdl(attn_bwd_tc16_kernel, dim3(grid), dim3(704), SMEM_BYTES, stream, tq, tdy, tdq, lse, delta,
                  static_cast<__nv_bfloat16*>(dqkv), T, H, scale, scale * 1.4426950408889634f);

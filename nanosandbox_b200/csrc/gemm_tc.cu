@@ -1141,6 +1141,36 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int esize, uint64_t d0, uint
   return 0;
 }
 
+// 3-D bf16 tensor [d2][d1 rows][d0 contiguous] (strides in elements), box {b0, b1, 1}, 128-byte swizzle: a store
+// through it is clipped at d1 inside every d2 slice (rows past a sequence's end are not written)
+int make_tmap_3d_bf16(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t row_stride,
+                      uint64_t slice_stride, uint32_t b0, uint32_t b1) {
+  NSB_REQUIRE(d1 < (1ull << 32) && d2 < (1ull << 31), "tensor map: dimensions too large");
+  MapKey key{ptr, d0, d1 + (d2 << 32), row_stride ^ (slice_stride << 20), b0, b1, 2u + 256u};
+  {
+    std::lock_guard<std::mutex> g(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return 0; }
+  }
+  EncodeTiledFn fn = get_encode_fn();
+  NSB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+  NSB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (row_stride * 2) % 16 == 0 && (slice_stride * 2) % 16 == 0,
+              "tensor map: operand must be 16-byte aligned with strides multiple of 16 bytes");
+  cuuint64_t gdim[3] = {d0, d1, d2};
+  cuuint64_t gstr[2] = {row_stride * 2, slice_stride * 2};
+  cuuint32_t box[3] = {b0, b1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  NSB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (3-D) failed with %d (dims %llu x %llu x %llu)", static_cast<int>(r),
+              static_cast<unsigned long long>(d0), static_cast<unsigned long long>(d1), static_cast<unsigned long long>(d2));
+  std::lock_guard<std::mutex> g(g_map_mu);
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps.emplace(key, *out);
+  return 0;
+}
+
 static long long* g_gemm_dbg = nullptr;
 static std::atomic<unsigned> g_sched_seq{0};
 static int g_dynamic_sched = 1;
