@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(192, 2)
 // Same pipeline as attn_fwd_tc_kernel; each query row is shared by two threads (64 key columns each), P always
 // lives in tensor memory, 80 registers per thread.  Warps: 0 TMA, 1 MMA issue, 2..9 softmax.
 __global__ void __launch_bounds__(320, 2)
-    attn_fwd_tc8_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ y,
+    attn_fwd_tc8_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_y,
                        float* __restrict__ lse, int Tn, int H, float scale_log2) {
   constexpr int p_in_tmem = 1;
   long long* const dbg = nullptr;
@@ -600,17 +600,24 @@ __global__ void __launch_bounds__(320, 2)
     ptx::mbar_wait(o_full, 0);
     ptx::tc_fence_after();
     {
+      // The O rows leave through the Q tile (free: every MMA has retired) and one TMA store, clipped at the end of
+      // the sequence.  Stored from registers -- 64 bytes per thread at a row stride of C -- a warp's store
+      // touches 32 lines and holds the load/store unit the SM's other CTA needs for its softmax.
       const float inv = 1.f / l;
-      const bool live = qi < Tn;                     // TMEM loads stay warp-collective; stores are predicated
-      uint4* dst = reinterpret_cast<uint4*>(y + (static_cast<size_t>(row_base) + (live ? qi : 0)) * C + h * HD + g * 32);
       float o[32];
       ptx::tmem_ld_32x32(o_addr, o);
-      if (live) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          dst[i] = make_uint4(pack_bf16x2(o[8 * i] * inv, o[8 * i + 1] * inv), pack_bf16x2(o[8 * i + 2] * inv, o[8 * i + 3] * inv),
-                              pack_bf16x2(o[8 * i + 4] * inv, o[8 * i + 5] * inv), pack_bf16x2(o[8 * i + 6] * inv, o[8 * i + 7] * inv));
-        if (g == 0) lse[(static_cast<size_t>(b) * H + h) * Tn + qi] = (m + log2f(l)) * 0.69314718055994531f;
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(sQ + sw128(row, g * 4 + i)) =
+            make_uint4(pack_bf16x2(o[8 * i] * inv, o[8 * i + 1] * inv), pack_bf16x2(o[8 * i + 2] * inv, o[8 * i + 3] * inv),
+                       pack_bf16x2(o[8 * i + 4] * inv, o[8 * i + 5] * inv), pack_bf16x2(o[8 * i + 6] * inv, o[8 * i + 7] * inv));
+      if (g == 0 && qi < Tn) lse[(static_cast<size_t>(b) * H + h) * Tn + qi] = (m + log2f(l)) * 0.69314718055994531f;
+      ptx::fence_proxy_async();
+      ptx::named_bar_sync(6, 256);                   // the eight softmax warps
+      if (threadIdx.x == 64) {
+        ptx::tma_store_3d(&tmap_y, sQ, h * HD, q0, b);
+        ptx::bulk_commit();
+        ptx::bulk_wait_read<0>();                    // the tile must outlive the read; the CTA exits below
       }
     }
   }
@@ -661,7 +668,10 @@ int attention_fwd_tc_launch(const void* qkv, void* y, float* lse, int B, int T, 
       cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
       NSB_REQUIRE(e == cudaSuccess, "attention_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     }
-    launch_pdl(attn_fwd_tc8_kernel, dim3(grid), dim3(320), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
+    CUtensorMap ty;
+    rc = make_tmap_3d_bf16(&ty, y, C, T, B, C, static_cast<uint64_t>(T) * C, HD, BQ);
+    if (rc) return rc;
+    launch_pdl(attn_fwd_tc8_kernel, dim3(grid), dim3(320), SMEM_BYTES, stream, tm, ty, lse, T, H,
                1.4426950408889634f / sqrtf(static_cast<float>(HD)));
   } else {
     launch_pdl(attn_fwd_tc_kernel, dim3(grid), dim3(192), SMEM_BYTES, stream, tm, static_cast<__nv_bfloat16*>(y), lse, T, H,
