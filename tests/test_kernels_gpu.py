@@ -470,9 +470,11 @@ def _attention_ref(qkv, B, T, H, D):
 
 
 @pytest.mark.parametrize("path", [0, 2])
-@pytest.mark.parametrize("B,T,H", [(2, 128, 3), (1, 1024, 2), (3, 100, 2), (2, 384, 4), (2, 64, 2)])
+@pytest.mark.parametrize("B,T,H", [(2, 128, 3), (1, 1024, 2), (3, 100, 2), (2, 384, 4), (2, 64, 2), (3, 1000, 12)])
 def test_attention_bf16_paths(path, B, T, H):
-    """tcgen05 forward (path 0) and the mma.sync flash kernels (path 2) against torch SDPA."""
+    """tcgen05 forward (path 0) and the mma.sync flash kernels (path 2) against torch SDPA.  The last shape has
+    288 (key block, head) items with a ragged last block: more than one per SM, so the persistent backward walks
+    several items per CTA (K / V double buffer, dK / dV hand-over between items, clipped TMA stores)."""
     lib = _lib.load()
     lib.nsb_attention_debug_config(path)
     try:
