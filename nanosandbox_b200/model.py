@@ -550,7 +550,12 @@ class GPT(nn.Module):
             ops.gemm_dynamic_tiles(True)
         main = torch.cuda.current_stream()
         side = None
-        if self.overlap_wgrad:
+        # A backward whose buckets are reduced as it goes keeps every weight-gradient GEMM on the compute stream: on
+        # 8 GPUs one replica was seen to drift from the others in a few rows of the LAST weight gradient of the first
+        # bucket (h.11.attn.c_attn; bench.py ddp_check) - the signature of that GEMM's
+        # accumulation landing after the bucket had been reduced and written back.  The side stream buys 0.3 % of a
+        # micro-step; one micro-step per optimizer step does without it.
+        if self.overlap_wgrad and not overlapped_comm:
             if self._wgrad_stream is None or self._wgrad_stream.device != main.device:
                 self._wgrad_stream = torch.cuda.Stream(device=main.device)
             side = self._wgrad_stream
