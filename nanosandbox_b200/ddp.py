@@ -47,6 +47,12 @@ class GradBucketManager:
         self.time_comm = False
         self.stub_collective = False    # measurement hook: skip the collective itself (pack / unpack still run)
         self.comm_info = {}
+        # NSB_DDP_VERIFY=1: after every synchronised backward, check that the gradient arena is the same bits on
+        # every rank (one checksum per bucket, one small all-reduce) and name the first bucket that is not: replicas
+        # stay identical only if it is, and the step at which they stop says what ran beside it
+        self.verify = os.environ.get("NSB_DDP_VERIFY", "0") == "1"
+        self.verify_steps = 0
+        self.verify_failures: List[dict] = []
 
     def all_reduce(self, t: torch.Tensor) -> None:
         if not self.stub_collective:
@@ -93,6 +99,31 @@ class GradBucketManager:
         assert self.launched == list(range(len(self.ranges))), \
             f"buckets reduced out of order or missing: {self.launched}"
         self.launched = []
+        if self.verify and not self.stub_collective:
+            self.verify_replicas()
+
+    def bucket_checksums(self) -> torch.Tensor:
+        """One int64 per bucket: the sum of the gradient words read as integers (any differing bit changes it,
+        up to cancellation)."""
+        words = self.grads.view(torch.int32)
+        return torch.stack([words[s:e].sum(dtype=torch.int64) for s, e in self.ranges])
+
+    def verify_replicas(self) -> bool:
+        """True when every rank holds the same gradient bits; otherwise records {step, buckets} in
+        verify_failures (and says so on stderr).  Costs one pass over the gradients: a debugging aid."""
+        mine = self.bucket_checksums()
+        lo, hi = mine.clone(), mine.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.pg)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.pg)
+        self.verify_steps += 1
+        bad = (lo != hi).nonzero().flatten().tolist()
+        if bad:
+            rec = {"step": self.verify_steps, "buckets": bad,
+                   "this_rank_differs_from_min": [k for k in bad if int(mine[k]) != int(lo[k])]}
+            self.verify_failures.append(rec)
+            import sys
+            print(f"nanosandbox_b200.ddp: synchronised gradients differ between ranks: {rec}", file=sys.stderr, flush=True)
+        return not bad
 
 
 def gradient_communicator(max_ctas: int):

@@ -113,3 +113,26 @@ def test_bucket_manager_mean_allreduce_both_payloads():
         assert res["bf16"] < 1e-2
         assert res["fp32_bytes"] == 1024 * 6 * 4 and res["bf16_bytes"] == 1024 * 6 * 2
         assert res["fp32_order_check"] and res["bf16_order_check"]
+
+
+def _verify_replicas(rank, world):
+    """GradBucketManager.verify_replicas: passes on identical gradients, names the bucket that differs."""
+    from nanosandbox_b200.ddp import GradBucketManager
+    n = 1024 * 6
+    ranges = [(0, 2048), (2048, 4096), (4096, n)]
+    grads = torch.arange(n, dtype=torch.float32) * 0.5
+    bk = GradBucketManager(grads, ranges, world, None, "fp32", scale=lambda g, inv: g.mul_(inv))
+    out = {"same": bk.verify_replicas()}
+    if rank == 1:
+        grads[3000] += 1e-3            # one element of bucket 1 on one rank
+    out["differs"] = not bk.verify_replicas()
+    out["record"] = bk.verify_failures[-1] if bk.verify_failures else None
+    return out
+
+
+def test_replica_verifier_names_the_bucket():
+    res = _spawn(_verify_replicas)
+    for r in res:
+        assert r["same"] and r["differs"]
+        assert r["record"]["buckets"] == [1] and r["record"]["step"] == 2
+    assert sorted(len(r["record"]["this_rank_differs_from_min"]) for r in res) == [0, 1]
